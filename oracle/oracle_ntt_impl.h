@@ -1,0 +1,80 @@
+/* ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.c). Included once per field with
+ *   FE    element type            FADD/FSUB/FMUL  field ops on the INTERNAL representation
+ *   NAME(x) symbol prefixing
+ * "values" is a slice of rows, each row = w consecutive field elements (w = 1: a plain [E];
+ * w = 8: the reference's [[B; 8]] segment rows, math/src/fft/fft_inputs.rs:151-207).
+ */
+
+/* math/src/fft/mod.rs:592-600 */
+static inline size_t NAME(permute_index)(size_t size, size_t index) {
+  unsigned bits = (unsigned)__builtin_ctzll((unsigned long long)size);
+  if (bits == 0) return 0;
+  size_t r = 0;
+  for (unsigned i = 0; i < bits; i++) r |= ((index >> i) & 1) << (bits - 1 - i);
+  return r;
+}
+
+/* math/src/fft/fft_inputs.rs:56-64 (permute): swap i <-> bitrev(i) when j > i */
+static void NAME(permute)(FE* v, size_t n, size_t w) {
+  for (size_t i = 0; i < n; i++) {
+    size_t j = NAME(permute_index)(n, i);
+    if (j > i)
+      for (size_t t = 0; t < w; t++) {
+        FE tmp = v[i * w + t];
+        v[i * w + t] = v[j * w + t];
+        v[j * w + t] = tmp;
+      }
+  }
+}
+
+/* math/src/fft/fft_inputs.rs:215-256: in-place recursive radix-2, natural in -> bit-reversed out,
+ * twiddles bit-reversed. n = number of rows. MAX_LOOP = 256 (fft_inputs.rs:10). */
+static void NAME(fft_rec)(FE* values, size_t n, size_t w, const FE* tw, size_t count, size_t stride, size_t offset) {
+  size_t size = n / stride;
+  if (size > 2) {
+    if (stride == count && count < 256) {
+      NAME(fft_rec)(values, n, w, tw, 2 * count, 2 * stride, offset);
+    } else {
+      NAME(fft_rec)(values, n, w, tw, count, 2 * stride, offset);
+      NAME(fft_rec)(values, n, w, tw, count, 2 * stride, offset + stride);
+    }
+  }
+  /* butterflies without twiddle (fft_inputs.rs:241-243, :106-112) */
+  for (size_t o = offset; o < offset + count; o++) {
+    FE* a = values + o * w;
+    FE* b = values + (o + stride) * w;
+    for (size_t t = 0; t < w; t++) {
+      FE x = a[t], y = b[t];
+      a[t] = FADD(x, y);
+      b[t] = FSUB(x, y);
+    }
+  }
+  /* butterflies with twiddles (fft_inputs.rs:246-255, :115-122) */
+  size_t last = offset + size * stride;
+  size_t i = 0;
+  for (size_t o = offset; o < last; o += 2 * stride, i++) {
+    if (i == 0) continue;
+    FE twd = tw[i];
+    for (size_t j = o; j < o + count; j++) {
+      FE* a = values + j * w;
+      FE* b = values + (j + stride) * w;
+      for (size_t t = 0; t < w; t++) {
+        FE x = a[t], y = FMUL(b[t], twd);
+        a[t] = FADD(x, y);
+        b[t] = FSUB(x, y);
+      }
+    }
+  }
+}
+static inline void NAME(fft_in_place)(FE* values, size_t n, size_t w, const FE* tw) {
+  if (n >= 2) NAME(fft_rec)(values, n, w, tw, 1, 1, 0);
+}
+
+/* math/src/utils/mod.rs:36-46: [1, b, b^2, ...] */
+static void NAME(power_series)(FE b, size_t n, FE one, FE* out) {
+  FE acc = one;
+  for (size_t i = 0; i < n; i++) {
+    out[i] = acc;
+    acc = FMUL(acc, b);
+  }
+}
