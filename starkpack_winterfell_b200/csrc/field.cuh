@@ -1,0 +1,311 @@
+// Field arithmetic for the trace-commitment path, host + device.
+//
+//   Gl64 : Goldilocks p = 2^64 - 2^32 + 1. The reference stores Montgomery words x*2^64 mod p
+//          (math/src/field/f64/mod.rs:48-53). The NTT is linear, so the kernels multiply those words by
+//          PLAIN-form twiddles with plain modular multiplication and the data stays in Montgomery form
+//          (SURVEY F5). All functions here are therefore plain arithmetic mod p on canonical inputs in
+//          [0,p), results canonical. `mont_red` is the reference's reduction (f64/mod.rs:651-661) used
+//          for as_int (hashing) and new.
+//   F128 : q = 2^128 - 45*2^40 + 1, canonical (math/src/field/f128/mod.rs:35,418-474).
+//
+// Everything is __host__ __device__ so the host plan builder (twiddle tables) and the CPU unit tests use
+// exactly the code the kernels run.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define WG_HD __host__ __device__ __forceinline__
+#else
+#define WG_HD inline
+#endif
+
+namespace wg {
+
+WG_HD void mul64wide(uint64_t a, uint64_t b, uint64_t& hi, uint64_t& lo) {
+#if defined(__CUDA_ARCH__)
+  lo = a * b;
+  hi = __umul64hi(a, b);
+#else
+  unsigned __int128 p = (unsigned __int128)a * b;
+  lo = (uint64_t)p;
+  hi = (uint64_t)(p >> 64);
+#endif
+}
+
+// ------------------------------------------------------------------------------------------------ Gl64
+struct Gl64 {
+  typedef uint64_t T;
+  static constexpr int kFieldId = 0;
+  static constexpr int kElemBytes = 8;
+  static constexpr int kTwoAdicity = 32;                         // f64/mod.rs:252
+  static constexpr uint64_t P = 0xFFFFFFFF00000001ULL;            // f64/mod.rs:37
+  static constexpr uint64_t EPS = 0xFFFFFFFFULL;                  // 2^64 mod p
+  static constexpr uint64_t ROOT_CANON = 7277203076849721926ULL;  // f64/mod.rs:264 (order 2^32)
+  static constexpr uint64_t GENERATOR_CANON = 7;                  // f64/mod.rs:248
+
+  static WG_HD T zero() { return 0; }
+  static WG_HD T one() { return 1; }
+  static WG_HD T from_u64(uint64_t v) { return v >= P ? v - P : v; }
+  static WG_HD bool is_zero(T a) { return a == 0; }
+
+  static WG_HD T add(T a, T b) {
+    uint64_t s = a + b;
+    // a,b < p: overflow past 2^64 or landing in [p, 2^64) both mean "subtract p" (== add EPS mod 2^64)
+    if (s < a || s >= P) s += EPS;
+    return s;
+  }
+  static WG_HD T sub(T a, T b) {
+    uint64_t d = a - b;
+    if (a < b) d -= EPS;  // + p
+    return d;
+  }
+  static WG_HD T neg(T a) { return a ? P - a : 0; }
+
+  // (hi*2^64 + lo) mod p, using 2^64 = 2^32 - 1 and 2^96 = -1
+  static WG_HD T reduce128(uint64_t hi, uint64_t lo) {
+    uint64_t hh = hi >> 32, hl = hi & EPS;
+    uint64_t t0 = lo - hh;
+    if (lo < hh) t0 -= EPS;
+    uint64_t t1 = hl * EPS;  // (hl << 32) - hl, < 2^64
+    uint64_t r = t0 + t1;
+    if (r < t0) r += EPS;
+    if (r >= P) r -= P;
+    return r;
+  }
+  static WG_HD T mul(T a, T b) {
+    uint64_t hi, lo;
+    mul64wide(a, b, hi, lo);
+    return reduce128(hi, lo);
+  }
+  // x * 2^k mod p for 0 <= k < 192 (2^96 = -1, 2^192 = 1). k is a compile-time constant at every call site.
+  static WG_HD T mul_pow2(T x, int k) {
+    bool negate = false;
+    if (k >= 96) {
+      k -= 96;
+      negate = true;
+    }
+    T r;
+    if (k == 0) {
+      r = x;
+    } else if (k < 64) {
+      r = reduce128(x >> (64 - k), x << k);
+    } else if (k == 64) {
+      r = reduce128(x, 0);
+    } else {
+      // x*2^k = w4*2^128 + hi*2^64, w4 = bits above 2^128; 2^128 = -2^32
+      int s = k - 64;
+      uint64_t hi = x << s, w4 = x >> (64 - s);  // w4 < 2^32
+      r = sub(reduce128(hi, 0), w4 << 32);       // w4<<32 <= 2^64 - 2^32 < p
+    }
+    return negate ? neg(r) : r;
+  }
+
+  // reference Montgomery reduction x*2^-64 mod p (f64/mod.rs:651-661), x = xh*2^64 + xl
+  static WG_HD uint64_t mont_red(uint64_t xh, uint64_t xl) {
+    uint64_t a = xl + (xl << 32);
+    uint64_t e = a < xl ? 1 : 0;
+    uint64_t b = a - (a >> 32) - e;
+    uint64_t r = xh - b;
+    if (xh < b) r -= EPS;
+    return r;
+  }
+  // internal word -> canonical integer (f64/mod.rs:275-282). Input any u64, output in [0,p).
+  static WG_HD uint64_t as_int(uint64_t w) { return mont_red(0, w); }
+  // canonical integer -> internal Montgomery word (f64/mod.rs:57-59): v * 2^64 mod p
+  static WG_HD uint64_t to_mont(uint64_t v) { return reduce128(v >= P ? v - P : v, 0); }
+
+  // w16^idx (forward) or w16^-idx (inverse) where w16 = 2^12 is the order-16 root matching ROOT_CANON
+  // (ROOT^(2^26) = 8, so w64 = 2^3).
+  template <bool INV>
+  static WG_HD T mul_root16(T x, int idx) {
+    idx &= 15;
+    int k = 12 * idx;
+    if (INV && idx) k = 192 - k;
+    return mul_pow2(x, k);
+  }
+};
+
+// ------------------------------------------------------------------------------------------------ F128
+struct u128 {
+  uint64_t lo, hi;
+};
+
+WG_HD bool u128_lt(u128 a, u128 b) { return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo); }
+WG_HD u128 u128_add(u128 a, u128 b, uint64_t& carry) {
+  u128 r;
+  r.lo = a.lo + b.lo;
+  uint64_t c0 = r.lo < a.lo ? 1 : 0;
+  uint64_t t = a.hi + b.hi;
+  uint64_t c1 = t < a.hi ? 1 : 0;
+  r.hi = t + c0;
+  uint64_t c2 = r.hi < t ? 1 : 0;
+  carry = c1 | c2;
+  return r;
+}
+WG_HD u128 u128_sub(u128 a, u128 b) {  // wrapping
+  u128 r;
+  r.lo = a.lo - b.lo;
+  r.hi = a.hi - b.hi - (a.lo < b.lo ? 1 : 0);
+  return r;
+}
+
+struct F128 {
+  typedef u128 T;
+  static constexpr int kFieldId = 1;
+  static constexpr int kElemBytes = 16;
+  static constexpr int kTwoAdicity = 40;                      // f128/mod.rs:169
+  static constexpr uint64_t M_LO = 0xFFFFD30000000001ULL;      // q = 2^128 - 45*2^40 + 1 (f128/mod.rs:35)
+  static constexpr uint64_t M_HI = 0xFFFFFFFFFFFFFFFFULL;
+  static constexpr uint64_t K = (45ULL << 40) - 1;             // 2^128 mod q
+  static constexpr uint64_t ROOT_LO = 0x86b8723e1920f4aaULL;   // 23953097886125630542083529559205016746
+  static constexpr uint64_t ROOT_HI = 0x120532e7b364080aULL;   // (f128/mod.rs:38), order 2^40
+  static constexpr uint64_t GENERATOR_CANON = 3;               // f128/mod.rs:165
+
+  static WG_HD T modulus() { return T{M_LO, M_HI}; }
+  static WG_HD T zero() { return T{0, 0}; }
+  static WG_HD T one() { return T{1, 0}; }
+  static WG_HD T from_u64(uint64_t v) { return T{v, 0}; }
+  static WG_HD bool is_zero(T a) { return (a.lo | a.hi) == 0; }
+  static WG_HD T canon(T a) { return u128_lt(a, modulus()) ? a : u128_sub(a, modulus()); }
+
+  static WG_HD T add(T a, T b) {
+    uint64_t c;
+    T s = u128_add(a, b, c);
+    // a,b < q: true sum < 2q. Subtract q when the sum overflowed 2^128 or is >= q.
+    if (c || !u128_lt(s, modulus())) s = u128_sub(s, modulus());
+    return s;
+  }
+  static WG_HD T sub(T a, T b) {
+    T d = u128_sub(a, b);
+    if (u128_lt(a, b)) {
+      uint64_t c;
+      d = u128_add(d, modulus(), c);
+    }
+    return d;
+  }
+  static WG_HD T neg(T a) { return is_zero(a) ? a : u128_sub(modulus(), a); }
+
+  // fold v = h*2^128 + l  ->  l + h*K (h < 2^64), returns 128-bit result plus carry word
+  static WG_HD T fold64(uint64_t h, T l, uint64_t& carry) {
+    uint64_t phi, plo;
+    mul64wide(h, K, phi, plo);
+    return u128_add(l, T{plo, phi}, carry);
+  }
+  static WG_HD T mul(T a, T b) {
+    // 256-bit schoolbook product w3..w0 (64-bit words)
+    uint64_t h00, l00, h01, l01, h10, l10, h11, l11;
+    mul64wide(a.lo, b.lo, h00, l00);
+    mul64wide(a.lo, b.hi, h01, l01);
+    mul64wide(a.hi, b.lo, h10, l10);
+    mul64wide(a.hi, b.hi, h11, l11);
+    uint64_t w0 = l00;
+    uint64_t w1 = h00 + l01;
+    uint64_t c1 = w1 < h00 ? 1 : 0;
+    w1 += l10;
+    c1 += w1 < l10 ? 1 : 0;
+    uint64_t w2 = h01 + h10;
+    uint64_t c2 = w2 < h01 ? 1 : 0;
+    w2 += l11;
+    c2 += w2 < l11 ? 1 : 0;
+    w2 += c1;
+    c2 += w2 < c1 ? 1 : 0;
+    uint64_t w3 = h11 + c2;
+    // value = (w3:w2)*2^128 + (w1:w0) == (w3:w2)*K + (w1:w0); K < 2^46
+    // (w3:w2)*K = w2*K + (w3*K << 64)
+    uint64_t p2h, p2l, p3h, p3l;
+    mul64wide(w2, K, p2h, p2l);
+    mul64wide(w3, K, p3h, p3l);
+    // t = (w1:w0) + (p2h:p2l) + (p3l << 64), overflow word o collects p3h and carries
+    uint64_t c;
+    T t = u128_add(T{w0, w1}, T{p2l, p2h}, c);
+    uint64_t o = p3h + c;  // p3h < 2^46
+    uint64_t th = t.hi + p3l;
+    o += th < t.hi ? 1 : 0;
+    t.hi = th;
+    // second fold: o < 2^47, o*K < 2^93
+    t = fold64(o, t, c);
+    // third fold: c in {0,1}; if it wrapped the remainder is tiny, so adding K cannot wrap again
+    if (c) {
+      uint64_t c2b;
+      t = u128_add(t, T{K, 0}, c2b);
+    }
+    return canon(t);
+  }
+  // w16^idx, w16 = ROOT^(2^36) (order 16); literals so the compiler folds them at unrolled call sites
+  static WG_HD T root16(int idx) {
+    switch (idx & 15) {
+      case 1: return T{0xab1ac6d8062c4665ULL, 0x9c511064995809f9ULL};
+      case 2: return T{0x21273cb06325d9a9ULL, 0xa2184c20306200b8ULL};
+      case 3: return T{0xb0d002c22bc23d17ULL, 0x2033e32141f648cdULL};
+      case 4: return T{0xbcb1099aefe38f3eULL, 0xab3b34a97d5ad72bULL};
+      case 5: return T{0x5b00e519a0a78877ULL, 0x39e874e797e3f285ULL};
+      case 6: return T{0x615afcf9833aa8e8ULL, 0xf6fdec9e92e80782ULL};
+      case 7: return T{0x5490ae4d6cef124cULL, 0x984cbf8ca1f67c30ULL};
+      case 8: return T{0xffffd30000000000ULL, 0xffffffffffffffffULL};
+      case 9: return T{0x54e50c27f9d3b99cULL, 0x63aeef9b66a7f606ULL};
+      case 10: return T{0xded8964f9cda2658ULL, 0x5de7b3dfcf9dff47ULL};
+      case 11: return T{0x4f2fd03dd43dc2eaULL, 0xdfcc1cdebe09b732ULL};
+      case 12: return T{0x434ec965101c70c3ULL, 0x54c4cb5682a528d4ULL};
+      case 13: return T{0xa4feede65f58778aULL, 0xc6178b18681c0d7aULL};
+      case 14: return T{0x9ea4d6067cc55719ULL, 0x090213616d17f87dULL};
+      case 15: return T{0xab6f24b29310edb5ULL, 0x67b340735e0983cfULL};
+      default: return T{1, 0};
+    }
+  }
+  template <bool INV>
+  static WG_HD T mul_root16(T x, int idx) {
+    idx &= 15;
+    if (idx == 0) return x;
+    if (idx == 8) return neg(x);
+    return mul(x, root16(INV ? 16 - idx : idx));
+  }
+};
+
+// ------------------------------------------------------------------------------------------------ generic helpers
+template <class F>
+WG_HD typename F::T f_pow(typename F::T b, uint64_t e) {
+  typename F::T r = F::one();
+  while (e) {
+    if (e & 1) r = F::mul(r, b);
+    b = F::mul(b, b);
+    e >>= 1;
+  }
+  return r;
+}
+// a^(p-2); only used on the host for n^-1 and inverse roots
+inline uint64_t gl64_inv(uint64_t a) { return f_pow<Gl64>(a, Gl64::P - 2); }
+inline u128 f128_inv(u128 a) {
+  // exponent q-2 = (M_HI:M_LO) - 2, square-and-multiply over 128 bits
+  u128 e = u128_sub(F128::modulus(), u128{2, 0});
+  u128 r = F128::one(), b = a;
+  for (int i = 0; i < 128; i++) {
+    uint64_t bit = i < 64 ? (e.lo >> i) & 1 : (e.hi >> (i - 64)) & 1;
+    if (bit) r = F128::mul(r, b);
+    b = F128::mul(b, b);
+  }
+  return r;
+}
+template <class F>
+inline typename F::T f_inv(typename F::T a);
+template <>
+inline uint64_t f_inv<Gl64>(uint64_t a) { return gl64_inv(a); }
+template <>
+inline u128 f_inv<F128>(u128 a) { return f128_inv(a); }
+
+// root of unity of order 2^log_n as a PLAIN field value (math/src/field/traits.rs:254-263)
+template <class F>
+inline typename F::T f_root_of_unity(int log_n);
+template <>
+inline uint64_t f_root_of_unity<Gl64>(int log_n) {
+  uint64_t r = Gl64::ROOT_CANON;
+  for (int i = 0; i < Gl64::kTwoAdicity - log_n; i++) r = Gl64::mul(r, r);
+  return r;
+}
+template <>
+inline u128 f_root_of_unity<F128>(int log_n) {
+  u128 r{F128::ROOT_LO, F128::ROOT_HI};
+  for (int i = 0; i < F128::kTwoAdicity - log_n; i++) r = F128::mul(r, r);
+  return r;
+}
+
+}  // namespace wg
