@@ -1,0 +1,119 @@
+/* winter_gpu.h — C ABI of the B200 trace-commitment library (libwinter_gpu.so).
+ *
+ * Drop-in boundary for ONE path of NethermindEth/starkpack-winterfell (reference = pure Rust, no FFI of
+ * its own): interpolate trace columns -> coset LDE -> hash LDE rows -> Merkle tree -> root. Each entry point
+ * replaces the body of the reference function cited beside it; a Rust `-sys` crate binds these symbols
+ * (see INTEGRATION.md). Plain pointers and sizes only; no torch / CUDA types in signatures (streams are
+ * passed as void*).
+ *
+ * Element encodings (exactly the reference's in-memory representation):
+ *   field 0 = f64 Goldilocks, one uint64 per element holding the MONTGOMERY word x*2^64 mod p
+ *             (math/src/field/f64/mod.rs:48-53); field 1 = f128, 16 bytes little-endian canonical
+ *             (math/src/field/f128/mod.rs:46-51).
+ *   hash  0 = Blake3_256 (crypto/src/hash/blake/mod.rs:20-60), 1 = Sha3_256 (crypto/src/hash/sha/mod.rs:17-57).
+ *   digests are 32 bytes.
+ * All functions return WG_OK (0) or a negative error code and are thread-safe. Precondition failures map to
+ * the reference's assert!/MerkleTreeError conditions. There is NO CPU fallback: without a CUDA device every
+ * compute entry point returns WG_ERR_CUDA.
+ */
+#ifndef WINTER_GPU_H
+#define WINTER_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  WG_OK = 0,
+  WG_ERR_NOT_POW2 = -1,     /* fft/mod.rs:90-105,279-295 "must be a power of 2"; MerkleTreeError::NumberOfLeavesNotPowerOfTwo */
+  WG_ERR_TOO_LARGE = -2,    /* log2(domain) > TWO_ADICITY (fft/mod.rs:291-295) or beyond this build's 2-pass limit (2^24) */
+  WG_ERR_ZERO_OFFSET = -3,  /* fft/mod.rs:197-200 "domain offset cannot be zero" */
+  WG_ERR_TOO_FEW = -4,      /* MerkleTreeError::TooFewLeaves (crypto/src/merkle/mod.rs:118-120) */
+  WG_ERR_ARG = -5,          /* null pointer / bad enum / twiddle length mismatch (fft/mod.rs:283-289) */
+  WG_ERR_CUDA = -6,         /* CUDA runtime error or no device; wg_last_error() has the text */
+  WG_ERR_NOMEM = -7,        /* device allocation failed / scratch too small */
+  WG_ERR_UNSUPPORTED = -8
+};
+
+enum { WG_FIELD_F64 = 0, WG_FIELD_F128 = 1 };
+enum { WG_HASH_BLAKE3_256 = 0, WG_HASH_SHA3_256 = 1 };
+
+/* Select the CUDA device for this process (one process per GPU). Idempotent. */
+int wg_init(int device);
+int wg_shutdown(void);
+/* Text of the last error on the calling thread. */
+const char* wg_last_error(void);
+/* Number of kernels this library has launched since wg_init (bench.py's gpu_launches). */
+uint64_t wg_launch_count(void);
+
+/* ---- host-buffer entry points (H2D + kernels + D2H inside) ------------------------------------------- */
+
+/* fft::get_twiddles / get_inv_twiddles (math/src/fft/mod.rs:466-482,505-522): n/2 elements, bit-reversed,
+ * internal representation. */
+int wg_get_twiddles(int field, uint64_t n, int inverse, void* out);
+
+/* fft::interpolate_poly (math/src/fft/mod.rs:274-305): in place, natural order in and out.
+ * inv_twiddles may be NULL; if given only its length contract (n/2) is assumed. */
+int wg_interpolate_poly(int field, void* evals, uint64_t n, const void* inv_twiddles);
+
+/* fft::evaluate_poly_with_offset (math/src/fft/mod.rs:171-220): out has n*blowup elements,
+ * out[k] = P(offset * w_{n*blowup}^k). offset points at one element in internal representation. */
+int wg_evaluate_poly_with_offset(int field, const void* p, uint64_t n, const void* twiddles, const void* offset,
+                                 uint64_t blowup, void* out);
+
+/* ColMatrix::interpolate_columns (prover/src/matrix/col_matrix.rs:196-206): columns are separate allocations. */
+int wg_interpolate_columns(int field, const void* const* columns, uint32_t n_cols, uint64_t n, void* const* polys_out);
+
+/* RowMatrix::evaluate_polys_over::<8> (prover/src/matrix/row_matrix.rs:82-133): out is row-major
+ * (n*blowup) x row_width, row_width = 8*ceil(n_cols/8), padding columns zero. offset = domain offset. */
+int wg_evaluate_polys_over(int field, const void* const* polys, uint32_t n_cols, uint64_t n, uint64_t blowup,
+                           const void* offset, void* out);
+
+/* RowMatrix::commit_to_rows leaves (row_matrix.rs:183-203; ElementHasher::hash_elements): one digest per row
+ * over the first elems_per_row elements of each row. */
+int wg_hash_rows(int field, int hash, const void* row_major, uint64_t rows, uint64_t row_width, uint64_t elems_per_row,
+                 uint8_t* leaves_out);
+
+/* MerkleTree::new -> build_merkle_nodes (crypto/src/merkle/mod.rs:117-136,350-374): nodes_out has n_leaves
+ * digests in heap layout (nodes[0] = 0, root = nodes[1]); adopt with MerkleTree::from_raw_parts (:149-161). */
+int wg_merkle_new(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t* nodes_out);
+
+/* Prover::build_trace_commitment (prover/src/lib.rs:615-670): T traces of n_rows rows, trace t has
+ * cols_per_trace[t] columns; column_ptrs lists all columns trace by trace. Domain offset = GENERATOR
+ * (air/src/options.rs:199-201). Outputs (each may be NULL): polys_out (same shape as column_ptrs),
+ * lde_out[t] row-major (n_rows*blowup) x 8*ceil(cols_t/8), leaves_out / nodes_out n_rows*blowup digests,
+ * root_out 32 bytes. */
+int wg_commit_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                    const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
+                    void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out);
+
+/* ---- device-resident entry points (no host transfers; what bench.py's `value` times) -------------------- */
+/* All pointers are device pointers on the wg_init device; `stream` is a cudaStream_t (NULL = default stream).
+ * Column matrices are contiguous: element (c, r) at [c*n + r]. */
+
+/* scratch elements (not bytes) needed by wg_interpolate_columns_dev / wg_lde_dev for these shapes */
+uint64_t wg_interpolate_scratch_elems(int field, uint32_t n_cols, uint64_t n);
+uint64_t wg_lde_scratch_elems(int field, uint32_t n_cols, uint64_t n, uint64_t blowup);
+
+int wg_interpolate_columns_dev(int field, const void* d_cols, uint32_t n_cols, uint64_t n, void* d_polys, void* d_scratch,
+                               uint64_t scratch_elems, void* stream);
+/* d_lde row-major (n*blowup) x row_width; columns n_cols..row_width-1 are written as zero. A smaller scratch
+ * than wg_lde_scratch_elems makes the call run in column chunks (minimum: 8 columns' worth). */
+int wg_lde_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset_host,
+               void* d_lde, uint64_t row_width, void* d_scratch, uint64_t scratch_elems, void* stream);
+/* leaves over the concatenation of n_traces row-major matrices (commit_to_comb_rows, row_matrix.rs:204-238) */
+int wg_hash_rows_dev(int field, int hash, uint32_t n_traces, const void* const* d_ldes, const uint64_t* row_widths,
+                     const uint64_t* elems_per_row, uint64_t rows, void* d_leaves, void* stream);
+int wg_merkle_dev(int hash, const void* d_leaves, uint64_t n_leaves, void* d_nodes, void* stream);
+/* whole commit on device: d_cols holds all columns of all traces contiguously ([sum cols][n_rows]);
+ * d_polys same shape; d_ldes[t] per trace; scratch as max of the two queries above. */
+int wg_commit_trace_dev(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                        const uint32_t* cols_per_trace, const void* d_cols, void* d_polys, void* const* d_ldes,
+                        void* d_leaves, void* d_nodes, void* d_scratch, uint64_t scratch_elems, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,83 @@
+"""ctypes binding of libwinter_gpu.so (C ABI: include/winter_gpu.h). The library is the product; there is no
+Python or CPU implementation behind these calls — if the shared object or a CUDA device is missing, every
+compute call raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libwinter_gpu.so")
+
+F64, F128 = 0, 1
+BLAKE3_256, SHA3_256 = 0, 1
+ELEM_BYTES = {F64: 8, F128: 16}
+
+WG_OK = 0
+ERR_NOT_POW2, ERR_TOO_LARGE, ERR_ZERO_OFFSET, ERR_TOO_FEW, ERR_ARG, ERR_CUDA, ERR_NOMEM, ERR_UNSUPPORTED = range(-1, -9, -1)
+
+# every symbol include/winter_gpu.h declares (tests check the .so exports all of them)
+SYMBOLS = [
+    "wg_init", "wg_shutdown", "wg_last_error", "wg_launch_count", "wg_get_twiddles", "wg_interpolate_poly",
+    "wg_evaluate_poly_with_offset", "wg_interpolate_columns", "wg_evaluate_polys_over", "wg_hash_rows", "wg_merkle_new",
+    "wg_commit_trace", "wg_interpolate_scratch_elems", "wg_lde_scratch_elems", "wg_interpolate_columns_dev",
+    "wg_lde_dev", "wg_hash_rows_dev", "wg_merkle_dev", "wg_commit_trace_dev",
+]
+
+
+class WinterGpuError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"winter_gpu error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def build():
+    """Compile the CUDA library in-tree (nvcc, sm_100a)."""
+    import subprocess
+
+    subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(_HERE, "csrc")])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise WinterGpuError(ERR_CUDA, f"{LIB_PATH} not built (run __graft_entry__.build()); there is no fallback path")
+        L = C.CDLL(LIB_PATH)
+        u64, u32, vp, i32 = C.c_uint64, C.c_uint32, C.c_void_p, C.c_int
+        L.wg_last_error.restype = C.c_char_p
+        L.wg_launch_count.restype = u64
+        L.wg_init.argtypes = [i32]
+        L.wg_get_twiddles.argtypes = [i32, u64, i32, vp]
+        L.wg_interpolate_poly.argtypes = [i32, vp, u64, vp]
+        L.wg_evaluate_poly_with_offset.argtypes = [i32, vp, u64, vp, vp, u64, vp]
+        L.wg_interpolate_columns.argtypes = [i32, vp, u32, u64, vp]
+        L.wg_evaluate_polys_over.argtypes = [i32, vp, u32, u64, u64, vp, vp]
+        L.wg_hash_rows.argtypes = [i32, i32, vp, u64, u64, u64, vp]
+        L.wg_merkle_new.argtypes = [i32, vp, u64, vp]
+        L.wg_commit_trace.argtypes = [i32, i32, u64, u64, u32, vp, vp, vp, vp, vp, vp, vp]
+        L.wg_interpolate_scratch_elems.restype = u64
+        L.wg_interpolate_scratch_elems.argtypes = [i32, u32, u64]
+        L.wg_lde_scratch_elems.restype = u64
+        L.wg_lde_scratch_elems.argtypes = [i32, u32, u64, u64]
+        L.wg_interpolate_columns_dev.argtypes = [i32, vp, u32, u64, vp, vp, u64, vp]
+        L.wg_lde_dev.argtypes = [i32, vp, u32, u64, u64, vp, vp, u64, vp, u64, vp]
+        L.wg_hash_rows_dev.argtypes = [i32, i32, u32, vp, vp, vp, u64, vp, vp]
+        L.wg_merkle_dev.argtypes = [i32, vp, u64, vp, vp]
+        L.wg_commit_trace_dev.argtypes = [i32, i32, u64, u64, u32, vp, vp, vp, vp, vp, vp, vp, u64, vp]
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != WG_OK:
+        raise WinterGpuError(rc, lib().wg_last_error().decode())
+
+
+def init(device=0):
+    check(lib().wg_init(device))
+
+
+def launch_count():
+    return int(lib().wg_launch_count())

@@ -1,0 +1,857 @@
+// C ABI (include/winter_gpu.h) and host-side orchestration of the trace-commitment path:
+//   Prover::build_trace_commitment (prover/src/lib.rs:615-670)
+//     = ColMatrix::interpolate_columns (col_matrix.rs:196-206)
+//     + RowMatrix::evaluate_polys_over::<8> (row_matrix.rs:82-133)
+//     + RowMatrix::commit_to_comb_rows (row_matrix.rs:204-238) -> MerkleTree::new (crypto/src/merkle/mod.rs:117-136)
+// Host code only builds small twiddle tables, picks pass shapes and launches kernels. There is no CPU
+// implementation of the path in this library.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/winter_gpu.h"
+#include "field.cuh"
+#include "hash.cuh"
+#include "hash_kernels.cuh"
+#include "ntt_launch.cuh"
+
+namespace wg {
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local std::string g_last_error;
+static std::atomic<uint64_t> g_launches{0};
+static int g_device = -1;
+static std::mutex g_mu;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+#define CUDA_TRY(expr)                                                                           \
+  do {                                                                                           \
+    cudaError_t e__ = (expr);                                                                    \
+    if (e__ != cudaSuccess) return fail(WG_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e__));  \
+  } while (0)
+#define WG_TRY(expr)          \
+  do {                        \
+    int rc__ = (expr);        \
+    if (rc__ != WG_OK) return rc__; \
+  } while (0)
+
+static inline bool is_pow2(uint64_t n) { return n && !(n & (n - 1)); }
+static inline int ilog2(uint64_t n) { return 63 - __builtin_clzll(n); }
+
+static int ensure_device() {
+  if (g_device < 0) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+      return fail(WG_ERR_CUDA, "no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_device < 0) g_device = 0;
+  }
+  CUDA_TRY(cudaSetDevice(g_device));
+  return WG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ tables
+// Small device-resident tables, built on the host with the same field code the kernels use, cached forever.
+template <class F>
+struct Tables {
+  typedef typename F::T T;
+  std::mutex mu;
+  std::map<std::pair<int, int>, T*> tws;                       // (log_s, inv) -> w_S^(+-e), e < S
+  struct Two {
+    T* lo = nullptr;
+    T* hi = nullptr;
+    int lb = 0;
+  };
+  std::map<std::pair<int, int>, Two> tm;                       // (log_n, inv) -> w_N^(+-e) two-level (inv: times n^-1)
+  std::map<std::tuple<int, int, uint64_t, uint64_t>, Two> pm;  // (log_n, log_b, offset) -> per-coset powers
+
+  static int upload(const std::vector<T>& h, T** out) {
+    T* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, h.size() * sizeof(T)));
+    CUDA_TRY(cudaMemcpy(d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = d;
+    return WG_OK;
+  }
+  static T root(int log_n, bool inv) {
+    T r = f_root_of_unity<F>(log_n);
+    return inv ? f_inv<F>(r) : r;
+  }
+
+  int get_tws(int log_s, bool inv, const T** out) {
+    std::lock_guard<std::mutex> lk(mu);
+    auto key = std::make_pair(log_s, (int)inv);
+    auto it = tws.find(key);
+    if (it == tws.end()) {
+      std::vector<T> h((size_t)1 << log_s);
+      T w = root(log_s, inv), acc = F::one();
+      for (auto& x : h) {
+        x = acc;
+        acc = F::mul(acc, w);
+      }
+      T* d;
+      WG_TRY(upload(h, &d));
+      it = tws.emplace(key, d).first;
+    }
+    *out = it->second;
+    return WG_OK;
+  }
+
+  // two-level power table of `base`: lo[e] = scale*base^e (e < 2^lb), hi[h] = base^(h << lb) (h < 2^(log_n-lb))
+  static void fill_two(T base, T scale, int log_n, int lb, T* lo, T* hi) {
+    T acc = scale;
+    for (size_t e = 0; e < ((size_t)1 << lb); e++) {
+      lo[e] = acc;
+      acc = F::mul(acc, base);
+    }
+    T step = f_pow<F>(base, (uint64_t)1 << lb);
+    acc = F::one();
+    for (size_t h = 0; h < ((size_t)1 << (log_n - lb)); h++) {
+      hi[h] = acc;
+      acc = F::mul(acc, step);
+    }
+  }
+
+  int get_tm(int log_n, bool inv, Two* out) {
+    std::lock_guard<std::mutex> lk(mu);
+    auto key = std::make_pair(log_n, (int)inv);
+    auto it = tm.find(key);
+    if (it == tm.end()) {
+      Two t;
+      t.lb = (log_n + 1) / 2;
+      std::vector<T> lo((size_t)1 << t.lb), hi((size_t)1 << (log_n - t.lb));
+      T scale = inv ? f_inv<F>(F::from_u64((uint64_t)1 << log_n)) : F::one();
+      fill_two(root(log_n, inv), scale, log_n, t.lb, lo.data(), hi.data());
+      WG_TRY(upload(lo, &t.lo));
+      WG_TRY(upload(hi, &t.hi));
+      it = tm.emplace(key, t).first;
+    }
+    *out = it->second;
+    return WG_OK;
+  }
+
+  // coset z of the LDE domain is offset * w_{N*B}^z; table z holds powers e < N of that base
+  int get_pm(int log_n, int log_b, T offset, Two* out, long long* zstride_lo, long long* zstride_hi) {
+    std::lock_guard<std::mutex> lk(mu);
+    uint64_t o_lo, o_hi;
+    memcpy(&o_lo, &offset, 8);
+    o_hi = 0;
+    if (sizeof(T) == 16) memcpy(&o_hi, (const char*)&offset + 8, 8);
+    auto key = std::make_tuple(log_n, log_b, o_lo, o_hi);
+    auto it = pm.find(key);
+    const int lb = log_n <= MAX_LOG_S ? log_n : (log_n + 1) / 2;
+    const size_t nlo = (size_t)1 << lb, nhi = (size_t)1 << (log_n - lb);
+    if (it == pm.end()) {
+      Two t;
+      t.lb = lb;
+      const size_t B = (size_t)1 << log_b;
+      std::vector<T> lo(nlo * B), hi(nhi * B);
+      T g = f_root_of_unity<F>(log_n + log_b);
+      T base = offset;
+      for (size_t z = 0; z < B; z++) {
+        fill_two(base, F::one(), log_n, lb, lo.data() + z * nlo, hi.data() + z * nhi);
+        base = F::mul(base, g);
+      }
+      WG_TRY(upload(lo, &t.lo));
+      WG_TRY(upload(hi, &t.hi));
+      it = pm.emplace(key, t).first;
+    }
+    *out = it->second;
+    *zstride_lo = (long long)nlo;
+    *zstride_hi = (long long)nhi;
+    return WG_OK;
+  }
+};
+
+template <class F>
+static Tables<F>& tables() {
+  static Tables<F> t;
+  return t;
+}
+
+template <class F>
+static int launch_pass(int layout, bool inv, int log_s, const PassArgs<F>& a, dim3 grid, cudaStream_t stream) {
+  cudaError_t e = launch_ntt_pass<F>(layout, inv, log_s, a, grid, stream);
+  if (e != cudaSuccess) return fail(WG_ERR_CUDA, "ntt pass launch (layout %d log_s %d): %s", layout, log_s, cudaGetErrorString(e));
+  g_launches++;
+  return WG_OK;
+}
+static inline unsigned cdiv(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+
+template <class F>
+static PassArgs<F> blank_args() {
+  PassArgs<F> a;
+  memset(&a, 0, sizeof a);
+  return a;
+}
+
+// split of a length-2^log_n transform: strided pass of 2^na points, then contiguous pass of 2^nb points
+static inline void split_passes(int log_n, int* na, int* nb) {
+  if (log_n <= MAX_LOG_S) {
+    *na = 0;
+    *nb = log_n;
+  } else {
+    *na = log_n / 2;
+    *nb = log_n - *na;
+  }
+}
+
+template <class F>
+static int check_domain(uint64_t n, uint64_t blowup) {
+  if (!is_pow2(n) || !is_pow2(blowup)) return fail(WG_ERR_NOT_POW2, "size %llu / blowup %llu must be powers of two", (unsigned long long)n, (unsigned long long)blowup);
+  if (n < 2) return fail(WG_ERR_ARG, "transform length must be at least 2");
+  if (ilog2(n) + ilog2(blowup) > F::kTwoAdicity) return fail(WG_ERR_TOO_LARGE, "domain 2^%d exceeds the field's two-adicity", ilog2(n) + ilog2(blowup));
+  if (ilog2(n) > 2 * MAX_LOG_S) return fail(WG_ERR_TOO_LARGE, "transform length above 2^%d is not supported by the two-pass plan", 2 * MAX_LOG_S);
+  return WG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ interpolate
+// c_j = n^-1 sum_k v_k w_n^(-jk), natural order in and out (math/src/fft/serial.rs:64-73), for n_cols
+// contiguous columns.
+template <class F>
+static uint64_t interpolate_scratch_elems(uint32_t n_cols, uint64_t n) {
+  return ilog2(n) <= MAX_LOG_S ? 0 : (uint64_t)n_cols * n;
+}
+
+template <class F>
+static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, uint64_t n, typename F::T* d_out,
+                                   typename F::T* d_scratch, uint64_t scratch_elems, cudaStream_t stream) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, 1));
+  if (n_cols == 0) return WG_OK;
+  if (n_cols > 65535) return fail(WG_ERR_UNSUPPORTED, "more than 65535 columns per call");
+  const int log_n = ilog2(n);
+  int na, nb;
+  split_passes(log_n, &na, &nb);
+  Tables<F>& tb = tables<F>();
+  if (na == 0) {
+    PassArgs<F> a = blank_args<F>();
+    a.in = d_in;
+    a.out = d_out;
+    a.in_wstride = (long long)n;
+    a.in_sstride = 1;
+    a.out_wstride = (long long)n;
+    a.out_jstride = 1;
+    a.nw_in = a.nw_out = n_cols;
+    WG_TRY(tb.get_tws(nb, true, &a.tws));
+    a.has_const = 1;
+    a.post_const = f_inv<F>(F::from_u64(n));
+    const int tw = 1 << pass_log_tw<F>(nb);
+    return launch_pass<F>(1, true, nb, a, dim3(cdiv(n_cols, tw), 1, 1), stream);
+  }
+  if (scratch_elems < (uint64_t)n_cols * n || !d_scratch) return fail(WG_ERR_NOMEM, "interpolate scratch too small");
+  const uint64_t K1 = (uint64_t)1 << na, K2 = (uint64_t)1 << nb;
+  typename Tables<F>::Two tm;
+  WG_TRY(tb.get_tm(log_n, true, &tm));
+  {  // pass A: for each k2, transform over k1 (stride K2); Y[mA*K2 + k2] *= n^-1 w_n^(-mA*k2)
+    PassArgs<F> a = blank_args<F>();
+    a.in = d_in;
+    a.out = d_scratch;
+    a.in_ystride = a.out_ystride = (long long)n;
+    a.in_wstride = a.out_wstride = 1;
+    a.in_sstride = a.out_jstride = (long long)K2;
+    a.nw_in = a.nw_out = (uint32_t)K2;
+    WG_TRY(tb.get_tws(na, true, &a.tws));
+    a.has_tm = 1;
+    a.tm_lo = tm.lo;
+    a.tm_hi = tm.hi;
+    a.tm_lb = tm.lb;
+    a.tm_mask = (uint32_t)(n - 1);
+    a.tm_w = 1;
+    const int tw = 1 << pass_log_tw<F>(na);
+    WG_TRY(launch_pass<F>(0, true, na, a, dim3(cdiv(K2, tw), n_cols, 1), stream));
+  }
+  {  // pass B: for each mA, transform over k2 (contiguous); c[mA + K1*mB]
+    PassArgs<F> a = blank_args<F>();
+    a.in = d_scratch;
+    a.out = d_out;
+    a.in_ystride = a.out_ystride = (long long)n;
+    a.in_wstride = (long long)K2;
+    a.in_sstride = 1;
+    a.out_wstride = 1;
+    a.out_jstride = (long long)K1;
+    a.nw_in = a.nw_out = (uint32_t)K1;
+    WG_TRY(tb.get_tws(nb, true, &a.tws));
+    const int tw = 1 << pass_log_tw<F>(nb);
+    WG_TRY(launch_pass<F>(1, true, nb, a, dim3(cdiv(K1, tw), n_cols, 1), stream));
+  }
+  return WG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ LDE
+// out[(k)*row_width + c] = P_c(offset * w_{nB}^k), k = j*B + z: coset z (shift offset*w_{nB}^z) evaluated at
+// w_n^j. Natural row order, row-major, pad columns zero (row_matrix.rs:82-133; segments.rs:53-207).
+template <class F>
+static uint64_t lde_scratch_elems(uint32_t n_cols, uint64_t n, uint64_t blowup) {
+  return ilog2(n) <= MAX_LOG_S ? 0 : (uint64_t)n_cols * n * blowup;
+}
+
+template <class F>
+static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, typename F::T offset,
+                   typename F::T* d_lde, uint64_t row_width, typename F::T* d_scratch, uint64_t scratch_elems,
+                   cudaStream_t stream) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, blowup));
+  if (F::is_zero(offset)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
+  if (row_width < n_cols) return fail(WG_ERR_ARG, "row_width < n_cols");
+  if (n_cols == 0) return WG_OK;
+  if (blowup > 65535) return fail(WG_ERR_UNSUPPORTED, "blowup too large");
+  const int log_n = ilog2(n), log_b = ilog2(blowup);
+  int na, nb;
+  split_passes(log_n, &na, &nb);
+  Tables<F>& tb = tables<F>();
+  typename Tables<F>::Two pm;
+  long long pzl, pzh;
+  WG_TRY(tb.get_pm(log_n, log_b, offset, &pm, &pzl, &pzh));
+  const uint32_t B = (uint32_t)blowup;
+  if (na == 0) {
+    PassArgs<F> a = blank_args<F>();
+    a.in = d_polys;
+    a.out = d_lde;
+    a.in_wstride = (long long)n;
+    a.in_sstride = 1;
+    a.out_wstride = 1;
+    a.out_zstride = (long long)row_width;
+    a.out_jstride = (long long)B * row_width;
+    a.nw_in = n_cols;
+    a.nw_out = (uint32_t)row_width;
+    WG_TRY(tb.get_tws(nb, false, &a.tws));
+    a.has_pm = 1;
+    a.pm_lo = pm.lo;
+    a.pm_hi = pm.hi;
+    a.pm_zstride_lo = pzl;
+    a.pm_zstride_hi = pzh;
+    a.pm_s = 1;
+    a.pm_w = 0;
+    a.pm_lb = pm.lb;
+    a.pm_mask = (uint32_t)(n - 1);
+    const int tw = 1 << pass_log_tw<F>(nb);
+    return launch_pass<F>(1, false, nb, a, dim3(cdiv(row_width, tw), 1, B), stream);
+  }
+  const uint64_t N1 = (uint64_t)1 << na, N2 = (uint64_t)1 << nb;
+  // columns per chunk limited by the scratch (B*n elements per column)
+  uint64_t chunk = scratch_elems / (n * blowup);
+  if (!d_scratch || chunk == 0) return fail(WG_ERR_NOMEM, "lde scratch too small");
+  if (chunk >= n_cols && row_width <= 65528) {
+    chunk = row_width;  // everything (pad columns included) in one sweep
+  } else {
+    if (chunk > 65528) chunk = 65528;
+    chunk = chunk / 8 * 8;
+    if (chunk == 0) return fail(WG_ERR_NOMEM, "lde scratch must hold at least 8 columns (8*n*blowup elements)");
+  }
+  typename Tables<F>::Two tm;
+  WG_TRY(tb.get_tm(log_n, false, &tm));
+  for (uint64_t c0 = 0; c0 < row_width; c0 += chunk) {
+    const uint32_t nc_out = (uint32_t)((row_width - c0) < chunk ? (row_width - c0) : chunk);  // incl. pad columns
+    const uint32_t nc_in = c0 >= n_cols ? 0 : (uint32_t)((n_cols - c0) < chunk ? (n_cols - c0) : chunk);
+    if (nc_in > 0) {
+      // pass A': coefficient m = m1*N2 + m2; scale by t_z^m, transform over m1 (stride N2),
+      // Z_z[c][j1*N2 + m2] *= w_n^(m2*j1)
+      PassArgs<F> a = blank_args<F>();
+      a.in = d_polys + c0 * n;
+      a.out = d_scratch;
+      a.in_ystride = (long long)n;
+      a.in_zstride = 0;
+      a.in_wstride = 1;
+      a.in_sstride = (long long)N2;
+      a.out_ystride = (long long)n;
+      a.out_zstride = (long long)nc_in * (long long)n;
+      a.out_wstride = 1;
+      a.out_jstride = (long long)N2;
+      a.nw_in = a.nw_out = (uint32_t)N2;
+      WG_TRY(tb.get_tws(na, false, &a.tws));
+      a.has_pm = 1;
+      a.pm_lo = pm.lo;
+      a.pm_hi = pm.hi;
+      a.pm_zstride_lo = pzl;
+      a.pm_zstride_hi = pzh;
+      a.pm_s = (uint32_t)N2;
+      a.pm_w = 1;
+      a.pm_lb = pm.lb;
+      a.pm_mask = (uint32_t)(n - 1);
+      a.has_tm = 1;
+      a.tm_lo = tm.lo;
+      a.tm_hi = tm.hi;
+      a.tm_lb = tm.lb;
+      a.tm_mask = (uint32_t)(n - 1);
+      a.tm_w = 1;
+      const int tw = 1 << pass_log_tw<F>(na);
+      WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw), nc_in, B), stream));
+    }
+    {
+      // pass B': for each (z, j1) transform over m2 (contiguous) -> rows (j1 + N1*j2)*B + z, columns c0..
+      PassArgs<F> a = blank_args<F>();
+      a.in = d_scratch;
+      a.out = d_lde + c0;
+      a.in_ystride = (long long)N2;
+      a.in_zstride = (long long)nc_in * (long long)n;
+      a.in_wstride = (long long)n;
+      a.in_sstride = 1;
+      a.out_ystride = (long long)B * row_width;
+      a.out_zstride = (long long)row_width;
+      a.out_wstride = 1;
+      a.out_jstride = (long long)N1 * B * row_width;
+      a.nw_in = nc_in;
+      a.nw_out = nc_out;
+      WG_TRY(tb.get_tws(nb, false, &a.tws));
+      const int tw = 1 << pass_log_tw<F>(nb);
+      WG_TRY(launch_pass<F>(1, false, nb, a, dim3(cdiv(nc_out, tw), (unsigned)N1, B), stream));
+    }
+  }
+  return WG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ hashing / Merkle
+template <class F>
+static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes, const uint64_t* row_widths,
+                         const uint64_t* elems, uint64_t rows, uint8_t* d_leaves, cudaStream_t stream) {
+  if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
+  if (hash != WG_HASH_BLAKE3_256 && hash != WG_HASH_SHA3_256) return fail(WG_ERR_ARG, "unknown hash %d", hash);
+  if (rows == 0) return WG_OK;
+  RowHashArgs a;
+  memset(&a, 0, sizeof a);
+  a.n_traces = n_traces;
+  a.rows = rows;
+  a.leaves = d_leaves;
+  uint64_t off = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    if (elems[t] > row_widths[t] || elems[t] == 0) return fail(WG_ERR_ARG, "elems_per_row must be in 1..row_width");
+    a.lde[t] = d_ldes[t];
+    a.row_width[t] = (uint32_t)row_widths[t];
+    a.unit_off[t] = (uint32_t)off;
+    off += elems[t] * (F::kElemBytes / 8);
+  }
+  if (off * 8 > (1u << 22)) return fail(WG_ERR_UNSUPPORTED, "rows longer than 4 MiB");
+  a.unit_off[n_traces] = (uint32_t)off;
+  const unsigned blocks = cdiv(rows, 32 * HASH_WARPS);
+  if (hash == WG_HASH_BLAKE3_256)
+    hash_rows_kernel<F, HASH_BLAKE3_256><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+  else
+    hash_rows_kernel<F, HASH_SHA3_256><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  return WG_OK;
+}
+
+template <int HASH>
+static int merkle_dev_t(const uint8_t* d_leaves, uint64_t n_leaves, uint8_t* d_nodes, cudaStream_t stream) {
+  uint4* nodes = reinterpret_cast<uint4*>(d_nodes);
+  uint64_t n = n_leaves / 2;
+  merkle_level_kernel<HASH><<<cdiv(n, 256), 256, 0, stream>>>(reinterpret_cast<const uint4*>(d_leaves), nodes + 2 * n, n);
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  while (n > 1024) {
+    merkle_level_kernel<HASH><<<cdiv(n / 2, 256), 256, 0, stream>>>(nodes + 2 * n, nodes + n, n / 2);
+    CUDA_TRY(cudaGetLastError());
+    g_launches++;
+    n /= 2;
+  }
+  merkle_top_kernel<HASH><<<1, 512, 0, stream>>>(nodes, (uint32_t)n);
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  return WG_OK;
+}
+
+static int merkle_dev(int hash, const uint8_t* d_leaves, uint64_t n_leaves, uint8_t* d_nodes, cudaStream_t stream) {
+  if (n_leaves < 2) return fail(WG_ERR_TOO_FEW, "a Merkle tree needs at least 2 leaves, got %llu", (unsigned long long)n_leaves);
+  if (!is_pow2(n_leaves)) return fail(WG_ERR_NOT_POW2, "number of leaves %llu is not a power of two", (unsigned long long)n_leaves);
+  if (hash == WG_HASH_BLAKE3_256) return merkle_dev_t<HASH_BLAKE3_256>(d_leaves, n_leaves, d_nodes, stream);
+  if (hash == WG_HASH_SHA3_256) return merkle_dev_t<HASH_SHA3_256>(d_leaves, n_leaves, d_nodes, stream);
+  return fail(WG_ERR_ARG, "unknown hash %d", hash);
+}
+
+// ------------------------------------------------------------------------------------------------ twiddles
+// get_twiddles / get_inv_twiddles (math/src/fft/mod.rs:466-482,505-522):
+// out[bitrev_{n/2}(i)] = internal(w_n^(+-i)), i < n/2; w_n^-i is read as w_n^(n-i) from the forward table.
+template <class F>
+__global__ void twiddles_kernel(typename F::T* out, uint32_t n, int log_half, int inverse, const typename F::T* lo,
+                                const typename F::T* hi, uint32_t lb) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n / 2) return;
+  const uint32_t e = inverse ? ((n - i) & (n - 1)) : i;
+  typename F::T v = table2<F>(lo, hi, lb, e);
+  const uint32_t j = log_half == 0 ? 0 : (__brev(i) >> (32 - log_half));
+  if (F::kFieldId == 0) {
+    uint64_t w;
+    memcpy(&w, &v, 8);
+    w = Gl64::to_mont(w);
+    memcpy(&v, &w, 8);
+  }
+  out[j] = v;
+}
+
+template <class F>
+static int get_twiddles_dev(uint64_t n, bool inverse, typename F::T* d_out, cudaStream_t stream) {
+  WG_TRY(check_domain<F>(n, 1));
+  const int log_n = ilog2(n);
+  typename Tables<F>::Two tm;
+  WG_TRY(tables<F>().get_tm(log_n, false, &tm));
+  twiddles_kernel<F><<<cdiv(n / 2, 256), 256, 0, stream>>>(d_out, (uint32_t)n, log_n - 1, inverse ? 1 : 0, tm.lo, tm.hi, tm.lb);
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  return WG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ whole commit
+template <class F>
+static typename F::T generator() {
+  return F::from_u64(F::GENERATOR_CANON);
+}
+template <class F>
+static typename F::T offset_from_internal(const void* p) {
+  typename F::T v;
+  memcpy(&v, p, sizeof v);
+  if (F::kFieldId == 0) {
+    uint64_t w;
+    memcpy(&w, &v, 8);
+    w = Gl64::as_int(w);  // Montgomery word -> plain value
+    memcpy(&v, &w, 8);
+  }
+  return v;
+}
+
+template <class F>
+static int commit_trace_dev(int hash, uint64_t n, uint64_t blowup, uint32_t n_traces, const uint32_t* cols_per_trace,
+                            const typename F::T* d_cols, typename F::T* d_polys, void* const* d_ldes, uint8_t* d_leaves,
+                            uint8_t* d_nodes, typename F::T* d_scratch, uint64_t scratch_elems, cudaStream_t stream) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, blowup));
+  if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
+  uint64_t total_cols = 0;
+  for (uint32_t t = 0; t < n_traces; t++) total_cols += cols_per_trace[t];
+  // interpolate_columns for every trace at once (columns are independent; prover/src/lib.rs:631-640)
+  for (uint64_t c0 = 0; c0 < total_cols; c0 += 65535) {
+    uint32_t nc = (uint32_t)((total_cols - c0) < 65535 ? (total_cols - c0) : 65535);
+    WG_TRY(interpolate_columns_dev<F>(d_cols + c0 * n, nc, n, d_polys + c0 * n, d_scratch, scratch_elems, stream));
+  }
+  // evaluate_polys_over::<8> per trace (prover/src/lib.rs:641-650), offset = GENERATOR (air/src/options.rs:199-201)
+  const void* ldes[HASH_MAX_TRACES];
+  uint64_t rws[HASH_MAX_TRACES], els[HASH_MAX_TRACES];
+  uint64_t c0 = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    const uint64_t rw = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
+    WG_TRY(lde_dev<F>(d_polys + c0 * n, cols_per_trace[t], n, blowup, generator<F>(), (T*)d_ldes[t], rw, d_scratch,
+                      scratch_elems, stream));
+    ldes[t] = d_ldes[t];
+    rws[t] = rw;
+    els[t] = cols_per_trace[t];
+    c0 += cols_per_trace[t];
+  }
+  // commit_to_comb_rows (row_matrix.rs:204-238)
+  WG_TRY(hash_rows_dev<F>(hash, n_traces, ldes, rws, els, n * blowup, d_leaves, stream));
+  return merkle_dev(hash, d_leaves, n * blowup, d_nodes, stream);
+}
+
+// RAII device buffer for the host-pointer entry points
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() {
+    if (p) cudaFree(p);
+  }
+  int alloc(size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+    }
+    return WG_OK;
+  }
+  template <class T>
+  T* as() { return reinterpret_cast<T*>(p); }
+};
+
+template <class F>
+static int h_get_twiddles(uint64_t n, int inverse, void* out) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, 1));
+  DevBuf d;
+  WG_TRY(d.alloc(n / 2 * sizeof(T)));
+  WG_TRY(get_twiddles_dev<F>(n, inverse != 0, d.as<T>(), 0));
+  CUDA_TRY(cudaMemcpy(out, d.p, n / 2 * sizeof(T), cudaMemcpyDeviceToHost));
+  return WG_OK;
+}
+
+template <class F>
+static int h_interpolate_columns(const void* const* cols, uint32_t n_cols, uint64_t n, void* const* outs) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, 1));
+  DevBuf in, out, scr;
+  const size_t colb = n * sizeof(T);
+  WG_TRY(in.alloc(colb * n_cols));
+  WG_TRY(out.alloc(colb * n_cols));
+  const uint64_t se = interpolate_scratch_elems<F>(n_cols, n);
+  WG_TRY(scr.alloc(se * sizeof(T)));
+  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(in.as<char>() + c * colb, cols[c], colb, cudaMemcpyHostToDevice, 0));
+  for (uint32_t c0 = 0; c0 < n_cols; c0 += 65535) {
+    uint32_t nc = (n_cols - c0) < 65535 ? (n_cols - c0) : 65535;
+    WG_TRY(interpolate_columns_dev<F>(in.as<T>() + (size_t)c0 * n, nc, n, out.as<T>() + (size_t)c0 * n, scr.as<T>(), se, 0));
+  }
+  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(outs[c], out.as<char>() + c * colb, colb, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+template <class F>
+static int h_evaluate_polys_over(const void* const* polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset,
+                                 void* out, uint64_t row_width) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, blowup));
+  DevBuf in, lde, scr;
+  const size_t colb = n * sizeof(T);
+  WG_TRY(in.alloc(colb * n_cols));
+  WG_TRY(lde.alloc(n * blowup * row_width * sizeof(T)));
+  const uint64_t se = lde_scratch_elems<F>(n_cols, n, blowup);
+  WG_TRY(scr.alloc(se * sizeof(T)));
+  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(in.as<char>() + c * colb, polys[c], colb, cudaMemcpyHostToDevice, 0));
+  WG_TRY(lde_dev<F>(in.as<T>(), n_cols, n, blowup, offset_from_internal<F>(offset), lde.as<T>(), row_width, scr.as<T>(), se, 0));
+  CUDA_TRY(cudaMemcpyAsync(out, lde.p, n * blowup * row_width * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+template <class F>
+static int h_hash_rows(int hash, const void* rows_host, uint64_t rows, uint64_t row_width, uint64_t elems, uint8_t* leaves) {
+  typedef typename F::T T;
+  DevBuf m, l;
+  WG_TRY(m.alloc(rows * row_width * sizeof(T)));
+  WG_TRY(l.alloc(rows * 32));
+  CUDA_TRY(cudaMemcpyAsync(m.p, rows_host, rows * row_width * sizeof(T), cudaMemcpyHostToDevice, 0));
+  const void* ptrs[1] = {m.p};
+  WG_TRY(hash_rows_dev<F>(hash, 1, ptrs, &row_width, &elems, rows, l.as<uint8_t>(), 0));
+  CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+template <class F>
+static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_traces, const uint32_t* cols_per_trace,
+                          const void* const* column_ptrs, void* const* polys_out, void* const* lde_out, uint8_t* leaves_out,
+                          uint8_t* nodes_out, uint8_t* root_out) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, blowup));
+  if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
+  uint64_t total_cols = 0, max_cols = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    total_cols += cols_per_trace[t];
+    if (cols_per_trace[t] > max_cols) max_cols = cols_per_trace[t];
+    if (cols_per_trace[t] == 0) return fail(WG_ERR_ARG, "trace %u has no columns", t);
+  }
+  const uint64_t L = n * blowup;
+  const size_t colb = n * sizeof(T);
+  DevBuf cols, polys, leaves, nodes, scr;
+  std::vector<DevBuf> ldes(n_traces);
+  WG_TRY(cols.alloc(colb * total_cols));
+  WG_TRY(polys.alloc(colb * total_cols));
+  WG_TRY(leaves.alloc(L * 32));
+  WG_TRY(nodes.alloc(L * 32));
+  uint64_t se = interpolate_scratch_elems<F>((uint32_t)total_cols, n);
+  const uint64_t se2 = lde_scratch_elems<F>((uint32_t)max_cols, n, blowup);
+  if (se2 > se) se = se2;
+  WG_TRY(scr.alloc(se * sizeof(T)));
+  std::vector<void*> lde_ptrs(n_traces);
+  for (uint32_t t = 0; t < n_traces; t++) {
+    const uint64_t rw = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
+    WG_TRY(ldes[t].alloc(L * rw * sizeof(T)));
+    lde_ptrs[t] = ldes[t].p;
+  }
+  for (uint64_t c = 0; c < total_cols; c++)
+    CUDA_TRY(cudaMemcpyAsync(cols.as<char>() + c * colb, column_ptrs[c], colb, cudaMemcpyHostToDevice, 0));
+  WG_TRY(commit_trace_dev<F>(hash, n, blowup, n_traces, cols_per_trace, cols.as<T>(), polys.as<T>(), lde_ptrs.data(),
+                             leaves.as<uint8_t>(), nodes.as<uint8_t>(), scr.as<T>(), se, 0));
+  if (polys_out)
+    for (uint64_t c = 0; c < total_cols; c++)
+      CUDA_TRY(cudaMemcpyAsync(polys_out[c], polys.as<char>() + c * colb, colb, cudaMemcpyDeviceToHost, 0));
+  if (lde_out)
+    for (uint32_t t = 0; t < n_traces; t++) {
+      const uint64_t rw = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
+      if (lde_out[t]) CUDA_TRY(cudaMemcpyAsync(lde_out[t], ldes[t].p, L * rw * sizeof(T), cudaMemcpyDeviceToHost, 0));
+    }
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves.p, L * 32, cudaMemcpyDeviceToHost, 0));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes.p, L * 32, cudaMemcpyDeviceToHost, 0));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes.as<uint8_t>() + 32, 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+}  // namespace wg
+
+// ================================================================================================ extern "C"
+using namespace wg;
+
+#define WG_FIELD_DISPATCH(field, CALL64, CALL128)                 \
+  do {                                                            \
+    if ((field) == WG_FIELD_F64) return CALL64;                   \
+    if ((field) == WG_FIELD_F128) return CALL128;                 \
+    return fail(WG_ERR_ARG, "unknown field id %d", (int)(field)); \
+  } while (0)
+
+extern "C" {
+
+int wg_init(int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return fail(WG_ERR_CUDA, "no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+  if (device < 0 || device >= n) return fail(WG_ERR_ARG, "device %d out of range (have %d)", device, n);
+  {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (g_device >= 0 && g_device != device)
+      return fail(WG_ERR_ARG, "library already bound to device %d (one process per GPU)", g_device);
+    g_device = device;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  return WG_OK;
+}
+
+int wg_shutdown(void) { return WG_OK; }  // tables live for the process lifetime
+
+const char* wg_last_error(void) { return g_last_error.c_str(); }
+uint64_t wg_launch_count(void) { return g_launches.load(); }
+
+int wg_get_twiddles(int field, uint64_t n, int inverse, void* out) {
+  if (!out) return fail(WG_ERR_ARG, "null output");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_get_twiddles<Gl64>(n, inverse, out), h_get_twiddles<F128>(n, inverse, out));
+}
+
+int wg_interpolate_poly(int field, void* evals, uint64_t n, const void* inv_twiddles) {
+  (void)inv_twiddles;  // the kernels keep their own on-chip twiddle tables
+  if (!evals) return fail(WG_ERR_ARG, "null input");
+  WG_TRY(ensure_device());
+  const void* in[1] = {evals};
+  void* out[1] = {evals};
+  WG_FIELD_DISPATCH(field, h_interpolate_columns<Gl64>(in, 1, n, out), h_interpolate_columns<F128>(in, 1, n, out));
+}
+
+int wg_evaluate_poly_with_offset(int field, const void* p, uint64_t n, const void* twiddles, const void* offset,
+                                 uint64_t blowup, void* out) {
+  (void)twiddles;
+  if (!p || !offset || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  const void* in[1] = {p};
+  WG_FIELD_DISPATCH(field, h_evaluate_polys_over<Gl64>(in, 1, n, blowup, offset, out, 1),
+                    h_evaluate_polys_over<F128>(in, 1, n, blowup, offset, out, 1));
+}
+
+int wg_interpolate_columns(int field, const void* const* columns, uint32_t n_cols, uint64_t n, void* const* polys_out) {
+  if (!columns || !polys_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_interpolate_columns<Gl64>(columns, n_cols, n, polys_out),
+                    h_interpolate_columns<F128>(columns, n_cols, n, polys_out));
+}
+
+int wg_evaluate_polys_over(int field, const void* const* polys, uint32_t n_cols, uint64_t n, uint64_t blowup,
+                           const void* offset, void* out) {
+  if (!polys || !offset || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  const uint64_t rw = (uint64_t)(n_cols + 7) / 8 * 8;
+  WG_FIELD_DISPATCH(field, h_evaluate_polys_over<Gl64>(polys, n_cols, n, blowup, offset, out, rw),
+                    h_evaluate_polys_over<F128>(polys, n_cols, n, blowup, offset, out, rw));
+}
+
+int wg_hash_rows(int field, int hash, const void* row_major, uint64_t rows, uint64_t row_width, uint64_t elems_per_row,
+                 uint8_t* leaves_out) {
+  if (!row_major || !leaves_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_hash_rows<Gl64>(hash, row_major, rows, row_width, elems_per_row, leaves_out),
+                    h_hash_rows<F128>(hash, row_major, rows, row_width, elems_per_row, leaves_out));
+}
+
+int wg_merkle_new(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t* nodes_out) {
+  if (!leaves || !nodes_out) return fail(WG_ERR_ARG, "null pointer");
+  if (n_leaves < 2) return fail(WG_ERR_TOO_FEW, "a Merkle tree needs at least 2 leaves, got %llu", (unsigned long long)n_leaves);
+  if (!is_pow2(n_leaves)) return fail(WG_ERR_NOT_POW2, "number of leaves %llu is not a power of two", (unsigned long long)n_leaves);
+  WG_TRY(ensure_device());
+  DevBuf l, nd;
+  WG_TRY(l.alloc(n_leaves * 32));
+  WG_TRY(nd.alloc(n_leaves * 32));
+  CUDA_TRY(cudaMemcpyAsync(l.p, leaves, n_leaves * 32, cudaMemcpyHostToDevice, 0));
+  WG_TRY(merkle_dev(hash, l.as<uint8_t>(), n_leaves, nd.as<uint8_t>(), 0));
+  CUDA_TRY(cudaMemcpyAsync(nodes_out, nd.p, n_leaves * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_commit_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                    const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
+                    void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out) {
+  if (!cols_per_trace || !column_ptrs) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field,
+                    h_commit_trace<Gl64>(hash, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out,
+                                         leaves_out, nodes_out, root_out),
+                    h_commit_trace<F128>(hash, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out,
+                                         leaves_out, nodes_out, root_out));
+}
+
+// ---- device-resident
+uint64_t wg_interpolate_scratch_elems(int field, uint32_t n_cols, uint64_t n) {
+  if (!is_pow2(n)) return 0;
+  return field == WG_FIELD_F64 ? interpolate_scratch_elems<Gl64>(n_cols, n) : interpolate_scratch_elems<F128>(n_cols, n);
+}
+uint64_t wg_lde_scratch_elems(int field, uint32_t n_cols, uint64_t n, uint64_t blowup) {
+  if (!is_pow2(n)) return 0;
+  return field == WG_FIELD_F64 ? lde_scratch_elems<Gl64>(n_cols, n, blowup) : lde_scratch_elems<F128>(n_cols, n, blowup);
+}
+
+int wg_interpolate_columns_dev(int field, const void* d_cols, uint32_t n_cols, uint64_t n, void* d_polys, void* d_scratch,
+                               uint64_t scratch_elems, void* stream) {
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field,
+                    interpolate_columns_dev<Gl64>((const uint64_t*)d_cols, n_cols, n, (uint64_t*)d_polys, (uint64_t*)d_scratch, scratch_elems, s),
+                    interpolate_columns_dev<F128>((const u128*)d_cols, n_cols, n, (u128*)d_polys, (u128*)d_scratch, scratch_elems, s));
+}
+
+int wg_lde_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset_host,
+               void* d_lde, uint64_t row_width, void* d_scratch, uint64_t scratch_elems, void* stream) {
+  if (!offset_host) return fail(WG_ERR_ARG, "null offset");
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field,
+                    lde_dev<Gl64>((const uint64_t*)d_polys, n_cols, n, blowup, offset_from_internal<Gl64>(offset_host), (uint64_t*)d_lde, row_width, (uint64_t*)d_scratch, scratch_elems, s),
+                    lde_dev<F128>((const u128*)d_polys, n_cols, n, blowup, offset_from_internal<F128>(offset_host), (u128*)d_lde, row_width, (u128*)d_scratch, scratch_elems, s));
+}
+
+int wg_hash_rows_dev(int field, int hash, uint32_t n_traces, const void* const* d_ldes, const uint64_t* row_widths,
+                     const uint64_t* elems_per_row, uint64_t rows, void* d_leaves, void* stream) {
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field, hash_rows_dev<Gl64>(hash, n_traces, d_ldes, row_widths, elems_per_row, rows, (uint8_t*)d_leaves, s),
+                    hash_rows_dev<F128>(hash, n_traces, d_ldes, row_widths, elems_per_row, rows, (uint8_t*)d_leaves, s));
+}
+
+int wg_merkle_dev(int hash, const void* d_leaves, uint64_t n_leaves, void* d_nodes, void* stream) {
+  WG_TRY(ensure_device());
+  return merkle_dev(hash, (const uint8_t*)d_leaves, n_leaves, (uint8_t*)d_nodes, (cudaStream_t)stream);
+}
+
+int wg_commit_trace_dev(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                        const uint32_t* cols_per_trace, const void* d_cols, void* d_polys, void* const* d_ldes,
+                        void* d_leaves, void* d_nodes, void* d_scratch, uint64_t scratch_elems, void* stream) {
+  if (!cols_per_trace || !d_cols || !d_polys || !d_ldes || !d_leaves || !d_nodes) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field,
+                    commit_trace_dev<Gl64>(hash, n_rows, blowup, n_traces, cols_per_trace, (const uint64_t*)d_cols, (uint64_t*)d_polys, d_ldes, (uint8_t*)d_leaves, (uint8_t*)d_nodes, (uint64_t*)d_scratch, scratch_elems, s),
+                    commit_trace_dev<F128>(hash, n_rows, blowup, n_traces, cols_per_trace, (const u128*)d_cols, (u128*)d_polys, d_ldes, (uint8_t*)d_leaves, (uint8_t*)d_nodes, (u128*)d_scratch, scratch_elems, s));
+}
+
+}  // extern "C"

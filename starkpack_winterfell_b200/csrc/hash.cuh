@@ -101,49 +101,69 @@ WG_HD void b3_merge(const uint32_t in16[16], uint32_t out[8]) {
   b3_compress(out, in16, 0, 64, B3_CHUNK_START | B3_CHUNK_END | B3_ROOT);
 }
 
-// Digest of `nbytes` (multiple of 4) delivered by ld(word_index) -> uint32 (little-endian words).
+// Streaming BLAKE3 over an input of known length: feed() takes consecutive 64-byte blocks (zero padded).
 // Single-chunk inputs (<= 1024 B: every config except 2^24 x 256) never touch the cv stack.
 constexpr int B3_MAX_STACK = 12;  // rows up to 4 MiB
-template <class LD>
-WG_HD void b3_hash_words(LD ld, uint32_t nbytes, uint32_t out[8]) {
-  const uint32_t nchunks = nbytes <= 1024 ? 1 : (nbytes + 1023) / 1024;
-  uint32_t stack[B3_MAX_STACK][8];
-  int sp = 0;
+struct B3Stream {
   uint32_t cv[8];
-  for (uint32_t c = 0; c < nchunks; c++) {
+  uint32_t stack[B3_MAX_STACK][8];
+  int sp;
+  uint32_t nbytes, pos, nchunks;
+  WG_HD void init(uint32_t nbytes_) {
+    nbytes = nbytes_;
+    pos = 0;
+    sp = 0;
+    nchunks = nbytes <= 1024 ? 1 : (nbytes + 1023) / 1024;
+  }
+  WG_HD bool done() const { return pos > 0 && pos >= nbytes; }
+  WG_HD void feed(const uint32_t m[16]) {
+    const uint32_t c = pos >> 10, off = pos & 1023;
     const uint32_t chunk_bytes = (nbytes - c * 1024) < 1024 ? (nbytes - c * 1024) : 1024;
-    const uint32_t nblocks = chunk_bytes == 0 ? 1 : (chunk_bytes + 63) / 64;
-    b3_iv(cv);
-    for (uint32_t b = 0; b < nblocks; b++) {
-      const uint32_t blen = (chunk_bytes - 64 * b) < 64 ? (chunk_bytes - 64 * b) : 64;
-      uint32_t flags = (b == 0 ? B3_CHUNK_START : 0) | (b == nblocks - 1 ? B3_CHUNK_END : 0);
-      if (nchunks == 1 && b == nblocks - 1) flags |= B3_ROOT;
-      uint32_t m[16];
-      const uint32_t w0 = c * 256 + b * 16;
-      const uint32_t nw = blen / 4;
-#pragma unroll
-      for (int i = 0; i < 16; i++) m[i] = (uint32_t)i < nw ? ld(w0 + i) : 0u;
-      b3_compress(cv, m, c, blen, flags);
-    }
-    if (c + 1 < nchunks) {
-      uint32_t total = c + 1;
-      while ((total & 1) == 0) {
-        sp--;
-        b3_parent(stack[sp], cv, 0);
-        total >>= 1;
-      }
-#pragma unroll
-      for (int i = 0; i < 8; i++) stack[sp][i] = cv[i];
-      sp++;
-    } else {
-      while (sp > 0) {
-        sp--;
-        b3_parent(stack[sp], cv, sp == 0 ? B3_ROOT : 0);
+    const bool last_in_chunk = off + 64 >= chunk_bytes;
+    const uint32_t blen = last_in_chunk ? chunk_bytes - off : 64;
+    uint32_t flags = (off == 0 ? B3_CHUNK_START : 0) | (last_in_chunk ? B3_CHUNK_END : 0);
+    if (nchunks == 1 && last_in_chunk) flags |= B3_ROOT;
+    if (off == 0) b3_iv(cv);
+    b3_compress(cv, m, c, blen, flags);
+    pos += 64;
+    if (last_in_chunk && nchunks > 1) {
+      if (c + 1 < nchunks) {
+        uint32_t total = c + 1;
+        while ((total & 1) == 0) {
+          sp--;
+          b3_parent(stack[sp], cv, 0);
+          total >>= 1;
+        }
+        for (int i = 0; i < 8; i++) stack[sp][i] = cv[i];
+        sp++;
+        pos = (c + 1) << 10;
+      } else {
+        while (sp > 0) {
+          sp--;
+          b3_parent(stack[sp], cv, sp == 0 ? B3_ROOT : 0);
+        }
+        pos = nbytes;
       }
     }
   }
+};
+
+// Digest of `nbytes` (multiple of 4) delivered by ld(word_index) -> uint32 (little-endian words).
+template <class LD>
+WG_HD void b3_hash_words(LD ld, uint32_t nbytes, uint32_t out[8]) {
+  B3Stream st;
+  st.init(nbytes);
+  const uint32_t nwords = nbytes / 4;
+  uint32_t w0 = 0;
+  do {
+    uint32_t m[16];
 #pragma unroll
-  for (int i = 0; i < 8; i++) out[i] = cv[i];
+    for (int i = 0; i < 16; i++) m[i] = (w0 + i) < nwords ? ld(w0 + i) : 0u;
+    st.feed(m);
+    w0 += 16;
+  } while (w0 < nwords);
+#pragma unroll
+  for (int i = 0; i < 8; i++) out[i] = st.cv[i];
 }
 
 // ------------------------------------------------------------------------------------------------ SHA3-256
@@ -156,7 +176,7 @@ WG_HD void keccak_f1600(uint64_t s[25]) {
                            0x000000008000808bULL, 0x800000000000008bULL, 0x8000000000008089ULL, 0x8000000000008003ULL,
                            0x8000000000008002ULL, 0x8000000000000080ULL, 0x000000000000800aULL, 0x800000008000000aULL,
                            0x8000000080008081ULL, 0x8000000000008080ULL, 0x0000000080000001ULL, 0x8000000080008008ULL};
-#pragma unroll 1
+#pragma unroll
   for (int round = 0; round < 24; round++) {
     uint64_t c0 = s[0] ^ s[5] ^ s[10] ^ s[15] ^ s[20];
     uint64_t c1 = s[1] ^ s[6] ^ s[11] ^ s[16] ^ s[21];

@@ -1,0 +1,179 @@
+// Leaf hashing and Merkle reduction kernels for sm_100a.
+//
+//   hash_rows_kernel  : RowMatrix::commit_to_rows / commit_to_comb_rows leaves
+//                       (prover/src/matrix/row_matrix.rs:183-238): leaf_k = H(row_k(t0)[0..C0] || row_k(t1)[0..C1] ..)
+//                       with every f64 element serialised canonically (as_int, math/src/field/f64/mod.rs:605-610)
+//                       and f128 as raw little-endian memory (f128/mod.rs:107-112); padding columns are skipped.
+//   merkle_level_kernel / merkle_top_kernel : MerkleTree::new -> build_merkle_nodes
+//                       (crypto/src/merkle/mod.rs:117-136,350-374): heap layout, nodes[0] = 0, root = nodes[1].
+//
+// Row hashing is integer-pipe bound (about 900 instructions per 64-byte BLAKE3 block), so one lane owns one
+// row and keeps the whole compression state in registers; a warp stages 128-byte (BLAKE3) / 136-byte (SHA3
+// rate) slabs of its 32 rows through shared memory so global loads stay coalesced and the Montgomery ->
+// canonical conversion happens once per element on the way in.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "field.cuh"
+#include "hash.cuh"
+
+namespace wg {
+
+constexpr int HASH_MAX_TRACES = 16;
+
+struct RowHashArgs {
+  const void* lde[HASH_MAX_TRACES];      // row-major matrices
+  uint32_t row_width[HASH_MAX_TRACES];   // elements per stored row (padded)
+  uint32_t unit_off[HASH_MAX_TRACES + 1];  // prefix sums of hashed 8-byte units per row
+  uint32_t n_traces;
+  uint64_t rows;
+  uint8_t* leaves;  // rows x 32 bytes
+};
+
+constexpr int HASH_WARPS = 8;
+
+template <class F, int HASH>
+__global__ void __launch_bounds__(HASH_WARPS * 32) hash_rows_kernel(const RowHashArgs A) {
+  constexpr int SU = HASH == HASH_BLAKE3_256 ? 16 : 17;  // 8-byte units per slab
+  constexpr int PITCH = 2 * SU + 1;                      // words; odd => conflict-free row reads
+  __shared__ uint32_t slab_all[HASH_WARPS][32 * PITCH];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  uint32_t* slab = slab_all[wid];
+  const uint64_t row0 = ((uint64_t)blockIdx.x * HASH_WARPS + wid) * 32;
+  if (row0 >= A.rows) return;
+  const uint32_t units_total = A.unit_off[A.n_traces];
+  const uint32_t nbytes = units_total * 8;
+
+  B3Stream b3;
+  uint64_t ks[25];
+  if (HASH == HASH_BLAKE3_256) {
+    b3.init(nbytes);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 25; i++) ks[i] = 0;
+  }
+  bool sha_done = false;
+
+  for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done); u0 += SU) {
+    // ---- stage SU units of each of the warp's 32 rows
+    for (int idx = lane; idx < 32 * SU; idx += 32) {
+      const int r = idx / SU, u = idx - r * SU;
+      const uint32_t gu = u0 + u;
+      const uint64_t row = row0 + r;
+      uint64_t v = 0;
+      if (gu < units_total && row < A.rows) {
+        uint32_t t = 0;
+        while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
+        const uint32_t lu = gu - A.unit_off[t];
+        if (F::kFieldId == 0) {
+          const uint64_t* p = (const uint64_t*)A.lde[t];
+          v = Gl64::as_int(p[row * A.row_width[t] + lu]);
+        } else {
+          const uint64_t* p = (const uint64_t*)A.lde[t];
+          v = p[row * A.row_width[t] * 2 + lu];
+        }
+      }
+      slab[r * PITCH + 2 * u] = (uint32_t)v;
+      slab[r * PITCH + 2 * u + 1] = (uint32_t)(v >> 32);
+    }
+    __syncwarp();
+    // ---- consume: lane owns row `lane`
+    const uint32_t* my = slab + lane * PITCH;
+    if (HASH == HASH_BLAKE3_256) {
+#pragma unroll 1
+      for (int b = 0; b < 2; b++) {
+        if ((u0 + 8 * b) * 8 < nbytes || (nbytes == 0 && b == 0)) {
+          uint32_t m[16];
+#pragma unroll
+          for (int i = 0; i < 16; i++) m[i] = my[16 * b + i];
+          b3.feed(m);
+        }
+      }
+    } else {
+      const uint32_t rem = units_total - u0 < 17u ? units_total - u0 : 17u;  // units_total >= u0 here
+#pragma unroll
+      for (int i = 0; i < 17; i++) {
+        uint64_t v = (uint64_t)my[2 * i] | ((uint64_t)my[2 * i + 1] << 32);
+        if (rem < 17u) {  // final (padded) block; staged units beyond `rem` are zero
+          if ((uint32_t)i == rem) v ^= 0x06ULL;
+          if (i == 16) v ^= 0x8000000000000000ULL;
+        }
+        ks[i] ^= v;
+      }
+      keccak_f1600(ks);
+      if (rem < 17u) sha_done = true;
+    }
+    __syncwarp();
+  }
+  const uint64_t row = row0 + lane;
+  if (row < A.rows) {
+    uint4* dst = reinterpret_cast<uint4*>(A.leaves + row * 32);
+    if (HASH == HASH_BLAKE3_256) {
+      dst[0] = make_uint4(b3.cv[0], b3.cv[1], b3.cv[2], b3.cv[3]);
+      dst[1] = make_uint4(b3.cv[4], b3.cv[5], b3.cv[6], b3.cv[7]);
+    } else {
+      dst[0] = make_uint4((uint32_t)ks[0], (uint32_t)(ks[0] >> 32), (uint32_t)ks[1], (uint32_t)(ks[1] >> 32));
+      dst[1] = make_uint4((uint32_t)ks[2], (uint32_t)(ks[2] >> 32), (uint32_t)ks[3], (uint32_t)(ks[3] >> 32));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- Merkle
+template <int HASH>
+__device__ __forceinline__ void merge64(const uint32_t in16[16], uint32_t out[8]) {
+  if (HASH == HASH_BLAKE3_256) {
+    b3_merge(in16, out);
+  } else {
+    sha3_256_lanes([&](uint32_t i) { return (uint64_t)in16[2 * i] | ((uint64_t)in16[2 * i + 1] << 32); }, 64, out);
+  }
+}
+
+// parents[i] = H(children[2i] || children[2i+1]), i < n_parents
+template <int HASH>
+__global__ void __launch_bounds__(256) merkle_level_kernel(const uint4* __restrict__ children, uint4* __restrict__ parents,
+                                                           uint64_t n_parents) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_parents) return;
+  uint32_t m[16], o[8];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    uint4 v = children[4 * i + k];
+    m[4 * k] = v.x;
+    m[4 * k + 1] = v.y;
+    m[4 * k + 2] = v.z;
+    m[4 * k + 3] = v.w;
+  }
+  merge64<HASH>(m, o);
+  parents[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
+  parents[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+}
+
+// Finishes the tree in one block: nodes[n .. 2n) hold level n (n <= 1024 a power of two); computes
+// nodes[n/2 .. n), ..., nodes[1], and zeroes nodes[0].
+template <int HASH>
+__global__ void __launch_bounds__(512) merkle_top_kernel(uint4* nodes, uint32_t n) {
+  for (uint32_t lvl = n / 2; lvl >= 1; lvl >>= 1) {
+    for (uint32_t i = threadIdx.x; i < lvl; i += blockDim.x) {
+      const uint32_t node = lvl + i;
+      uint32_t m[16], o[8];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        uint4 v = nodes[2 * (2 * node) + k];
+        m[4 * k] = v.x;
+        m[4 * k + 1] = v.y;
+        m[4 * k + 2] = v.z;
+        m[4 * k + 3] = v.w;
+      }
+      merge64<HASH>(m, o);
+      nodes[2 * node] = make_uint4(o[0], o[1], o[2], o[3]);
+      nodes[2 * node + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    nodes[0] = make_uint4(0, 0, 0, 0);
+    nodes[1] = make_uint4(0, 0, 0, 0);
+  }
+}
+
+}  // namespace wg

@@ -1,0 +1,286 @@
+// Batched shared-memory NTT pass for sm_100a.
+//
+// One kernel template covers every NTT-shaped step of the trace commitment:
+//   * ColMatrix::interpolate_columns  (prover/src/matrix/col_matrix.rs:196-206 -> fft::interpolate_poly,
+//     math/src/fft/mod.rs:274, serial.rs:64-73)
+//   * RowMatrix::evaluate_polys_over  (prover/src/matrix/row_matrix.rs:82-133, segments.rs:53-207)
+//   * fft::evaluate_poly_with_offset  (math/src/fft/mod.rs:171, serial.rs:26-57)
+// The reference runs an in-place radix-2 network with bit-reversed output, then a permutation pass (and for
+// the matrix a transpose). Field arithmetic is exact, so any algorithm gives the same words; here a
+// length-N transform is split N = K1*K2 into at most two passes over HBM, each pass a batch of length-S
+// (S <= 4096) transforms done entirely on chip:
+//     - thread-level radix-16/8/4/2 butterflies in registers (for Goldilocks the inner twiddles are powers of
+//       two because w64 = 8, so they are shifts, not multiplications),
+//     - digit exchange through shared memory between register steps, twiddles w_S^e read from a shared table,
+//     - first step loads straight from HBM, last step stores straight to HBM in NATURAL order, so no
+//       permutation pass and no transpose exist.
+// A tile is S transform points x TW independent problems. LAYOUT 0 ("strided pass"): the TW problems are
+// contiguous in memory (coalesced 64-byte pieces), the transform runs along a stride. LAYOUT 1 ("contiguous
+// pass"): the transform runs along contiguous memory, the TW problems are strided on input and contiguous
+// on output (this is what writes row-major LDE rows, 8 columns = one 64-byte row segment per store).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "field.cuh"
+
+namespace wg {
+
+template <class F>
+struct PassArgs {
+  typedef typename F::T T;
+  const T* in;
+  T* out;
+  // element offsets: blockIdx.y*ystride + blockIdx.z*zstride + wg*wstride + s*sstride   (wg = global w index)
+  long long in_ystride, in_zstride, in_wstride, in_sstride;
+  long long out_ystride, out_zstride, out_wstride, out_jstride;
+  uint32_t nw_in;   // problems with wg >= nw_in read as zero
+  uint32_t nw_out;  // problems with wg >= nw_out are not written
+  // in-block twiddles w_S^(+-e), e < S
+  const T* tws;
+  // optional pre-multiplication x[s] *= PM^(s*pm_s + wg*pm_w)  (two-level table, per-z tables)
+  const T* pm_lo;
+  const T* pm_hi;
+  long long pm_zstride_lo, pm_zstride_hi;
+  uint32_t pm_s, pm_w, pm_lb, pm_mask;  // exponent & pm_mask, lo index = e & ((1<<pm_lb)-1)
+  // optional post-multiplication X[j] *= TM^(j * (wg*tm_w + y*tm_y))  (two-level table)
+  const T* tm_lo;
+  const T* tm_hi;
+  uint32_t tm_w, tm_y, tm_lb, tm_mask;
+  // optional constant post-scale (n^-1 when no tm table carries it)
+  T post_const;
+  int has_pm, has_tm, has_const;
+};
+
+// ---------------------------------------------------------------------------------------------- radix butterflies
+constexpr __host__ __device__ int bitrev_c(int x, int bits) {
+  int r = 0;
+  for (int i = 0; i < bits; i++) r |= ((x >> i) & 1) << (bits - 1 - i);
+  return r;
+}
+
+// natural-order in, natural-order out length-R transform of a[] held in registers (R = 2^LR, LR <= 4)
+template <class F, int LR, bool INV>
+__device__ __forceinline__ void radix_ntt(typename F::T (&a)[1 << LR]) {
+  typedef typename F::T T;
+  constexpr int R = 1 << LR;
+#pragma unroll
+  for (int half = R / 2; half >= 1; half >>= 1) {
+#pragma unroll
+    for (int g = 0; g < R; g += 2 * half) {
+#pragma unroll
+      for (int k = 0; k < half; k++) {
+        T x = a[g + k], y = a[g + k + half];
+        a[g + k] = F::add(x, y);
+        T d = F::sub(x, y);
+        a[g + k + half] = (k == 0) ? d : F::template mul_root16<INV>(d, k * (8 / half));
+      }
+    }
+  }
+  // DIF leaves X[bitrev(pos)] at pos
+  T b[R];
+#pragma unroll
+  for (int i = 0; i < R; i++) b[bitrev_c(i, LR)] = a[i];
+#pragma unroll
+  for (int i = 0; i < R; i++) a[i] = b[i];
+}
+
+// ---------------------------------------------------------------------------------------------- compile-time plan
+template <class F>
+struct FieldCfg;
+template <>
+struct FieldCfg<Gl64> {
+  static constexpr int MAXLR = 4;      // radix-16 register butterflies
+  static constexpr int LOG_TILE = 14;  // S*TW <= 2^14 elements (128 KB)
+  static constexpr int MAX_LOG_TW = 3;
+  static constexpr int PAD_LOG = 3;  // pad unit: 8 elements = 64 B
+};
+template <>
+struct FieldCfg<F128> {
+  static constexpr int MAXLR = 3;
+  static constexpr int LOG_TILE = 13;
+  static constexpr int MAX_LOG_TW = 2;
+  static constexpr int PAD_LOG = 2;  // 4 elements = 64 B
+};
+
+template <class F, int LOG_S, int LAYOUT>
+struct PassCfg {
+  typedef FieldCfg<F> FC;
+  static constexpr int MAXLR = FC::MAXLR;
+  static constexpr int NSTEPS = (LOG_S + MAXLR - 1) / MAXLR;
+  static constexpr int LOG_TW = (FC::LOG_TILE - LOG_S) < FC::MAX_LOG_TW ? (FC::LOG_TILE - LOG_S) : FC::MAX_LOG_TW;
+  static constexpr int TW = 1 << LOG_TW;
+  static constexpr int S = 1 << LOG_S;
+  static constexpr __host__ __device__ int lr(int u) { return u < NSTEPS - 1 ? MAXLR : LOG_S - MAXLR * (NSTEPS - 1); }
+  // log2 of the sub-problem size AFTER step u
+  static constexpr __host__ __device__ int logp(int u) {
+    int l = LOG_S;
+    for (int v = 0; v <= u; v++) l -= lr(v);
+    return l;
+  }
+  static constexpr int LR_LAST = LOG_S - MAXLR * (NSTEPS - 1);
+  // threads: one item (R elements) per thread per step where possible
+  static constexpr int ITEMS0 = (S >> (NSTEPS > 1 ? MAXLR : LOG_S)) * TW;
+  static constexpr int NT = ITEMS0 >= 512 ? 512 : (ITEMS0 <= 32 ? 32 : ITEMS0);
+  // shared-memory index of logical (s, w); padded against bank conflicts of the last register step
+  static constexpr int PAD_SHIFT = LAYOUT == 0 ? (LR_LAST + LOG_TW) : 7;
+  static constexpr int SP = S + ((S >> 7) << FC::PAD_LOG) + 1;  // LAYOUT 1 row pitch
+  static __host__ __device__ __forceinline__ int phys(int s, int w) {
+    if (LAYOUT == 0) {
+      int idx = s * TW + w;
+      return idx + ((idx >> PAD_SHIFT) << FC::PAD_LOG);
+    } else {
+      return w * SP + s + ((s >> 7) << FC::PAD_LOG);
+    }
+  }
+  static constexpr int TILE_ELEMS =
+      NSTEPS == 1 ? 0 : (LAYOUT == 0 ? (S * TW + (((S * TW) >> PAD_SHIFT) << FC::PAD_LOG)) : TW * SP);
+  static constexpr int TWS_ELEMS = NSTEPS == 1 ? 0 : S;
+  static constexpr size_t SMEM_BYTES = (size_t)(TILE_ELEMS + TWS_ELEMS) * sizeof(typename F::T);
+};
+
+template <class F>
+__device__ __forceinline__ typename F::T table2(const typename F::T* __restrict__ lo, const typename F::T* __restrict__ hi,
+                                                uint32_t lb, uint32_t e) {
+  typename F::T a = lo[e & ((1u << lb) - 1u)];
+  uint32_t h = e >> lb;
+  return h ? F::mul(a, hi[h]) : a;
+}
+
+// ---------------------------------------------------------------------------------------------- one register step
+template <class F, int LOG_S, int LAYOUT, bool INV, int U>
+__device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* tile, const typename F::T* tws,
+                                          long long in_base, long long out_base, uint32_t w0) {
+  typedef typename F::T T;
+  typedef PassCfg<F, LOG_S, LAYOUT> C;
+  constexpr int LR = C::lr(U);
+  constexpr int R = 1 << LR;
+  constexpr int LOGP = C::logp(U);       // sub-problem size after this step
+  constexpr int LOGPP = LOGP + LR;       // before this step
+  constexpr int LOGQ = LOG_S - LR;       // items per problem
+  constexpr bool FIRST = (U == 0), LAST = (U == C::NSTEPS - 1);
+  constexpr bool W_FASTEST = (LAYOUT == 0) || (LAST && !FIRST);
+  constexpr int NITEMS = (1 << LOGQ) * C::TW;
+
+  for (int item = threadIdx.x; item < NITEMS; item += C::NT) {
+    int q, w;
+    if (W_FASTEST) {
+      w = item & (C::TW - 1);
+      q = item >> C::LOG_TW;
+    } else {
+      q = item & ((1 << LOGQ) - 1);
+      w = item >> LOGQ;
+    }
+    const int blk = q >> LOGP;
+    const int m_rest = q & ((1 << LOGP) - 1);
+    const int s0 = (blk << LOGPP) + m_rest;  // element r lives at s0 + (r << LOGP)
+    const uint32_t wg = w0 + (uint32_t)w;
+    T a[R];
+    if (FIRST) {
+      if (wg < A.nw_in) {
+        const T* src = A.in + in_base + (long long)wg * A.in_wstride;
+#pragma unroll
+        for (int r = 0; r < R; r++) a[r] = src[(long long)(s0 + (r << LOGP)) * A.in_sstride];
+        if (A.has_pm) {
+          const T* lo = A.pm_lo + (long long)blockIdx.z * A.pm_zstride_lo;
+          const T* hi = A.pm_hi + (long long)blockIdx.z * A.pm_zstride_hi;
+#pragma unroll
+          for (int r = 0; r < R; r++) {
+            uint32_t e = ((uint32_t)(s0 + (r << LOGP)) * A.pm_s + wg * A.pm_w) & A.pm_mask;
+            if (e) a[r] = F::mul(a[r], table2<F>(lo, hi, A.pm_lb, e));
+          }
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < R; r++) a[r] = F::zero();
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < R; r++) a[r] = tile[C::phys(s0 + (r << LOGP), w)];
+    }
+
+    radix_ntt<F, LR, INV>(a);
+
+    if (!LAST) {
+      // twiddle w_{2^LOGPP}^(m_rest*j) = w_S^(m_rest*j << (LOG_S-LOGPP)); then scatter digit j
+#pragma unroll
+      for (int j = 0; j < R; j++) {
+        T v = a[j];
+        if (j > 0) v = F::mul(v, tws[(m_rest * j) << (LOG_S - LOGPP)]);
+        tile[C::phys(s0 + (j << LOGP), w)] = v;
+      }
+    } else {
+      // natural output index: digits j_0 (most significant in blk) ... j_{U-1}, then this step's j
+      int nat0 = 0, shift_out = 0, rem = blk;
+      {
+        // blk = sum_v j_v << (bits below v); walk from the least significant digit (step U-1) upwards
+        int widths[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int v = 0; v < U; v++) widths[v] = C::lr(v);
+        int pos[4] = {0, 0, 0, 0};
+        int acc = 0;
+#pragma unroll
+        for (int v = 0; v < U; v++) {
+          pos[v] = acc;  // weight of j_v in the natural index
+          acc += widths[v];
+        }
+        shift_out = acc;
+#pragma unroll
+        for (int v = U - 1; v >= 0; v--) {
+          int d = rem & ((1 << widths[v]) - 1);
+          rem >>= widths[v];
+          nat0 |= d << pos[v];
+        }
+      }
+      if (wg < A.nw_out) {
+        T* dst = A.out + out_base + (long long)wg * A.out_wstride;
+        uint32_t ebase = 0, estep = 0;
+        if (A.has_tm) {
+          uint32_t f = wg * A.tm_w + blockIdx.y * A.tm_y;
+          ebase = (uint32_t)nat0 * f;
+          estep = f << shift_out;
+        }
+#pragma unroll
+        for (int j = 0; j < R; j++) {
+          T v = a[j];
+          if (A.has_tm) {
+            uint32_t e = (ebase + (uint32_t)j * estep) & A.tm_mask;
+            v = F::mul(v, table2<F>(A.tm_lo, A.tm_hi, A.tm_lb, e));
+          } else if (A.has_const) {
+            v = F::mul(v, A.post_const);
+          }
+          dst[(long long)(nat0 + (j << shift_out)) * A.out_jstride] = v;
+        }
+      }
+    }
+  }
+}
+
+template <class F, int LOG_S, int LAYOUT, bool INV>
+__global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT) ntt_pass_kernel(const PassArgs<F> A) {
+  typedef typename F::T T;
+  typedef PassCfg<F, LOG_S, LAYOUT> C;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* tile = reinterpret_cast<T*>(smem_raw);
+  T* tws = tile + C::TILE_ELEMS;
+  if (C::NSTEPS > 1) {
+    for (int i = threadIdx.x; i < C::S; i += C::NT) tws[i] = A.tws[i];
+  }
+  const uint32_t w0 = blockIdx.x * C::TW;
+  const long long in_base = (long long)blockIdx.y * A.in_ystride + (long long)blockIdx.z * A.in_zstride;
+  const long long out_base = (long long)blockIdx.y * A.out_ystride + (long long)blockIdx.z * A.out_zstride;
+  pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, in_base, out_base, w0);
+  if (C::NSTEPS > 1) {
+    __syncthreads();
+    pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 1 ? 1 : 0)>(A, tile, tws, in_base, out_base, w0);
+  }
+  if (C::NSTEPS > 2) {
+    __syncthreads();
+    pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 2 ? 2 : 0)>(A, tile, tws, in_base, out_base, w0);
+  }
+  if (C::NSTEPS > 3) {
+    __syncthreads();
+    pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 3 ? 3 : 0)>(A, tile, tws, in_base, out_base, w0);
+  }
+}
+
+}  // namespace wg

@@ -1,0 +1,5 @@
+// Goldilocks instantiations of the NTT pass kernel.
+#include "ntt_launch.cuh"
+namespace wg {
+WG_DEFINE_LAUNCH_NTT_PASS(Gl64)
+}
