@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py — trace LDE + Merkle commit (BASELINE.json metric) on N B200s of one node.
+
+One "step" = one full Prover::build_trace_commitment pass (interpolate columns -> coset LDE -> hash LDE rows ->
+Merkle tree) over one synthetic trace. N=1 workload = BASELINE.json configs[1]: 2^22 rows x 100 Goldilocks
+columns, blowup 8, Blake3_256. N>1: every rank commits its own trace of that shape (independent traces, no
+data-path collective; "weak" scaling) — the StarkPack "one trace per GPU" partition of configs[3].
+
+  value        device-resident: trace already in HBM, results left in HBM, CUDA events around K steps
+  e2e          the same work through the C-ABI host entry point wg_commit_trace with pinned host buffers:
+               H2D of the trace and D2H of polys + LDE + leaves + nodes inside the timed region
+  roofline     dominant kernel (LDE contiguous pass), algorithmic bytes / its CUDA-event time
+  cpu_baseline the CPU oracle (C + OpenMP restatement of the reference, kind "port") on a bounded sample
+  --impl reference : that oracle as the reference arm, on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LOG_ROWS, COLS, BLOWUP = 22, 100, 8
+SEED = 0xC0FFEE02
+METRIC = "lde_merkle_commit_ms_2^22x100_f64_blowup8"
+
+
+def algorithmic_bytes(n, cols, blowup, esize=8):
+    """read trace + write polys + write LDE (unpadded) + write leaves + write nodes."""
+    L = n * blowup
+    return n * cols * esize * 2 + L * cols * esize + 2 * L * 32
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def synth_trace_device(torch, cols, n, seed, device):
+    """SURVEY 8(d) generator x(c, r) = splitmix64(seed + c*2^32 + r) reduced below p, computed on the GPU with
+    int64 wraparound arithmetic (identical words to tests/fixtures.synth_f64)."""
+    def lsr(x, k):
+        return (x >> k) & ((1 << (64 - k)) - 1)
+
+    def i64(v):
+        v &= (1 << 64) - 1
+        return v - (1 << 64) if v >> 63 else v
+
+    out = torch.empty((cols, n, 1), dtype=torch.int64, device=device)
+    r = torch.arange(n, dtype=torch.int64, device=device)
+    for c in range(cols):
+        z = r + i64(seed + (c << 32)) + i64(0x9E3779B97F4A7C15)
+        z = (z ^ lsr(z, 30)) * i64(0xBF58476D1CE4E5B9)
+        z = (z ^ lsr(z, 27)) * i64(0x94D049BB133111EB)
+        z = z ^ lsr(z, 31)
+        # unsigned z >= p  <=>  signed z in [p - 2^64, -1] = [-(2^32) + 1, -1]; subtracting p == adding 2^32 - 1
+        ge = (z < 0) & (z >= -(1 << 32) + 1)
+        out[c, :, 0] = torch.where(ge, z + ((1 << 32) - 1), z)
+    return out
+
+
+def cpu_commit_sample(log_rows_sample, steps=1, warmup=0):
+    """Times the CPU oracle (oracle/oracle.c, C + OpenMP restatement of the reference's concurrent path, kind
+    "port": no Rust toolchain here, so oracle/_ref does not exist) on a 2^log_rows_sample x 100 sample of the
+    workload with every host thread, and scales linearly in rows to the full 2^22 configuration."""
+    import numpy as np
+
+    import oracle
+    from tests import fixtures as fx
+
+    oracle.build()
+    n = 1 << log_rows_sample
+    tr = fx.synth_f64(SEED, COLS, n)
+    best = []
+    root = None
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = oracle.commit_trace(0, 0, [tr], BLOWUP, want=("nodes",))
+        dt = time.perf_counter() - t0
+        root = bytes(r["root"])
+        if i >= warmup:
+            best.append(dt)
+    ms_sample = 1e3 * sum(best) / len(best)
+    scale = (1 << LOG_ROWS) / n
+    return {"value": ms_sample * scale, "unit": "ms", "cores": int(oracle.lib().or_threads()), "kind": "port",
+            "sample": f"2^{log_rows_sample} rows x {COLS} cols f64 blowup {BLOWUP} Blake3_256, {ms_sample:.1f} ms measured, "
+                      f"scaled x{scale:g} (linear in rows) to 2^{LOG_ROWS}",
+            "sample_ms": ms_sample, "sample_root": root.hex()}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb = cpu_commit_sample(args.cpu_log_rows, steps=max(1, args.steps), warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "ms", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["sample_ms"], "higher_is_better": False,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit",
+                       "reference_arm": "CPU oracle port of the reference's concurrent path (Rust toolchain absent)"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_e2e(torch, w, dev, rank, world, steps, warmup, dist):
+    """wg_commit_trace through host buffers: pinned trace in, pinned polys + LDE + leaves + nodes out."""
+    import ctypes as C
+
+    import psutil
+
+    from starkpack_winterfell_b200._lib import check, lib
+
+    n, L = 1 << LOG_ROWS, (1 << LOG_ROWS) * BLOWUP
+    rw = (COLS + 7) // 8 * 8
+    need = (2 * n * COLS * 8 + L * rw * 8 + 2 * L * 32) * 1.15
+    with_lde = psutil.virtual_memory().available / max(world, 1) > need
+    pin = dict(dtype=torch.int64, pin_memory=True)
+    cols_h = torch.empty((COLS, n), **pin)
+    cols_h.copy_(synth_trace_device(torch, COLS, n, SEED + rank, dev)[:, :, 0])
+    polys_h = torch.empty((COLS, n), **pin)
+    lde_h = torch.empty((L, rw), **pin) if with_lde else None
+    leaves_h = torch.empty((L, 32), dtype=torch.uint8, pin_memory=True)
+    nodes_h = torch.empty((L, 32), dtype=torch.uint8, pin_memory=True)
+    root_h = torch.zeros(32, dtype=torch.uint8, pin_memory=True)
+    torch.cuda.synchronize()
+    colp = (C.c_void_p * COLS)(*[cols_h[c].data_ptr() for c in range(COLS)])
+    polp = (C.c_void_p * COLS)(*[polys_h[c].data_ptr() for c in range(COLS)])
+    ldep = (C.c_void_p * 1)(lde_h.data_ptr()) if with_lde else None
+    cpt = (C.c_uint32 * 1)(COLS)
+
+    def step():
+        check(lib().wg_commit_trace(w.F64, w.BLAKE3_256, n, BLOWUP, 1, cpt, colp, polp, ldep, C.c_void_p(leaves_h.data_ptr()),
+                                    C.c_void_p(nodes_h.data_ptr()), C.c_void_p(root_h.data_ptr())))
+
+    for _ in range(warmup):
+        step()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()  # synchronous: returns after the D2H copies have landed
+    torch.cuda.synchronize()
+    ms = 1e3 * (time.perf_counter() - t0) / steps
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    h2d = n * COLS * 8
+    d2h = n * COLS * 8 + (L * rw * 8 if with_lde else 0) + 2 * L * 32 + 32
+    return {"value": ms / world, "unit": "ms", "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h, "root": bytes(root_h.numpy()).hex(),
+            "outputs": "polys + LDE + leaves + nodes + root" if with_lde else "polys + leaves + nodes + root (LDE left on "
+            "device: host RAM too small for N pinned LDE buffers)", "timer": "host perf_counter around synchronous C-ABI calls"}
+
+
+def run_ours(args):
+    import torch
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist_mod.init_process_group("nccl", device_id=dev)
+        dist = dist_mod
+    import starkpack_winterfell_b200 as w
+    from starkpack_winterfell_b200 import _lib
+    from starkpack_winterfell_b200.device import TraceCommitter
+
+    n = 1 << LOG_ROWS
+    tc = TraceCommitter(w.F64, w.BLAKE3_256, n, BLOWUP, [COLS], device=dev)
+    tc.cols.copy_(synth_trace_device(torch, COLS, n, SEED + rank, dev))
+    W, K = max(args.warmup, 3), max(args.steps, 1)
+    for _ in range(W):
+        tc.commit()
+    torch.cuda.synchronize()
+    root_warm = tc.root()
+    _lib.profile_enable(True)
+    _lib.profile_read()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        tc.commit()
+    e1.record()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = e0.elapsed_time(e1) / K
+    launches = _lib.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    phases = {k: (v[0] / K, v[1] // K) for k, v in _lib.profile_read().items()}
+    _lib.profile_enable(False)
+    assert tc.root() == root_warm, "root changed between identical steps"
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    root_hex = tc.root().hex()
+    del tc
+    torch.cuda.empty_cache()
+    e2e = run_e2e(torch, w, dev, rank, world, steps=min(K, 2), warmup=1, dist=dist)
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    L = n * BLOWUP
+    rw = (COLS + 7) // 8 * 8
+    # dominant kernel = LDE contiguous pass (ntt_pass_kernel<Gl64,11,1,false>): its own compulsory traffic is
+    # one read of the B*N*C intermediate and one write of the L x C LDE words (DESIGN.md "kernels")
+    dom = max(phases, key=lambda k: phases[k][0])
+    kbytes = {"lde_contig": 2 * L * COLS * 8, "lde_strided": n * COLS * 8 + L * COLS * 8,
+              "interp_strided": 2 * n * COLS * 8, "interp_contig": 2 * n * COLS * 8,
+              "hash_rows": L * COLS * 8 + L * 32, "merkle": 2 * L * 32}[dom]
+    dom_ms = phases[dom][0] / max(phases[dom][1], 1)
+    achieved = kbytes / (dom_ms * 1e-3) / 1e9
+    alg = algorithmic_bytes(n, COLS, BLOWUP)
+    cb = cpu_commit_sample(args.cpu_log_rows) if world == 1 else None
+    line = {
+        "metric": METRIC, "value": ms / world, "unit": "ms", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms,
+        "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit, "
+                               f"one trace per GPU", "l2": "inputs (3.4 GB trace, 27 GB LDE) far exceed the 126 MB L2; no flush needed",
+                   "value_is": "ms per committed trace = ms_per_step / n_gpus"},
+        "lde_rows_per_s": world * L / (ms * 1e-3), "trace_rows_per_s": world * n / (ms * 1e-3),
+        "commit_roofline": {"algorithmic_bytes": alg, "achieved_gbs": alg / (ms * 1e-3) / 1e9, "frac": alg / (ms * 1e-3) / 1e9 / peak},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "root": root_hex,
+        "phases_ms": {k: round(v[0], 3) for k, v in phases.items()},
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": kbytes, "kernel_ms": dom_ms,
+                     "note": "integer-issue bound, see DESIGN.md; HBM fraction reported as the contract asks"},
+        "cpu_baseline": cb,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-log-rows", type=int, default=18, help="rows (log2) of the CPU baseline sample")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -48,6 +48,13 @@ const char* wg_last_error(void);
 /* Number of kernels this library has launched since wg_init (bench.py's gpu_launches). */
 uint64_t wg_launch_count(void);
 
+/* Phase timing (CUDA events on the launching stream) of the device-resident entry points. Phases:
+ * 0 interpolate strided pass, 1 interpolate contiguous pass, 2 LDE strided pass, 3 LDE contiguous pass,
+ * 4 row hashing, 5 Merkle. wg_profile_read waits for the recorded work, writes summed milliseconds and the
+ * number of timed launches-groups per phase into 6-entry arrays, and clears the records. */
+int wg_profile_enable(int on);
+int wg_profile_read(float* ms_out, uint32_t* count_out);
+
 /* ---- host-buffer entry points (H2D + kernels + D2H inside) ------------------------------------------- */
 
 /* fft::get_twiddles / get_inv_twiddles (math/src/fft/mod.rs:466-482,505-522): n/2 elements, bit-reversed,

@@ -16,7 +16,7 @@ ERR_NOT_POW2, ERR_TOO_LARGE, ERR_ZERO_OFFSET, ERR_TOO_FEW, ERR_ARG, ERR_CUDA, ER
 
 # every symbol include/winter_gpu.h declares (tests check the .so exports all of them)
 SYMBOLS = [
-    "wg_init", "wg_shutdown", "wg_last_error", "wg_launch_count", "wg_get_twiddles", "wg_interpolate_poly",
+    "wg_init", "wg_shutdown", "wg_last_error", "wg_launch_count", "wg_profile_enable", "wg_profile_read", "wg_get_twiddles", "wg_interpolate_poly",
     "wg_evaluate_poly_with_offset", "wg_interpolate_columns", "wg_evaluate_polys_over", "wg_hash_rows", "wg_merkle_new",
     "wg_commit_trace", "wg_interpolate_scratch_elems", "wg_lde_scratch_elems", "wg_interpolate_columns_dev",
     "wg_lde_dev", "wg_hash_rows_dev", "wg_merkle_dev", "wg_commit_trace_dev",
@@ -77,6 +77,21 @@ def check(rc):
 
 def init(device=0):
     check(lib().wg_init(device))
+
+
+PHASES = ["interp_strided", "interp_contig", "lde_strided", "lde_contig", "hash_rows", "merkle"]
+
+
+def profile_enable(on=True):
+    check(lib().wg_profile_enable(1 if on else 0))
+
+
+def profile_read():
+    """-> {phase: (ms_total, n_records)} since the last read (synchronises)."""
+    ms = (C.c_float * 6)()
+    cnt = (C.c_uint32 * 6)()
+    check(lib().wg_profile_read(ms, cnt))
+    return {PHASES[i]: (float(ms[i]), int(cnt[i])) for i in range(6)}
 
 
 def launch_count():

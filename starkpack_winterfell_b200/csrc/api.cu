@@ -194,6 +194,41 @@ static int launch_pass(int layout, bool inv, int log_s, const PassArgs<F>& a, di
 }
 static inline unsigned cdiv(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
 
+// ------------------------------------------------------------------------------------------------ phase timing
+// Optional CUDA-event timing of the phases of a commit, on the launching stream (bench.py's roofline figure).
+enum { PH_INTERP_A = 0, PH_INTERP_B, PH_LDE_A, PH_LDE_B, PH_HASH, PH_MERKLE, PH_COUNT };
+struct ProfRec {
+  int phase;
+  cudaEvent_t a, b;
+};
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static std::vector<cudaEvent_t> g_prof_pool;
+static cudaEvent_t prof_event() {
+  cudaEvent_t e;
+  if (!g_prof_pool.empty()) {
+    e = g_prof_pool.back();
+    g_prof_pool.pop_back();
+  } else {
+    cudaEventCreate(&e);
+  }
+  return e;
+}
+struct ProfScope {
+  int idx = -1;
+  cudaStream_t s;
+  ProfScope(int phase, cudaStream_t stream) : s(stream) {
+    if (!g_prof_on) return;
+    ProfRec r{phase, prof_event(), prof_event()};
+    cudaEventRecord(r.a, s);
+    g_prof.push_back(r);
+    idx = (int)g_prof.size() - 1;
+  }
+  ~ProfScope() {
+    if (idx >= 0) cudaEventRecord(g_prof[idx].b, s);
+  }
+};
+
 template <class F>
 static PassArgs<F> blank_args() {
   PassArgs<F> a;
@@ -253,6 +288,7 @@ static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, u
     a.has_const = 1;
     a.post_const = f_inv<F>(F::from_u64(n));
     const int tw = 1 << pass_log_tw<F>(nb);
+    ProfScope ps(PH_INTERP_B, stream);
     return launch_pass<F>(1, true, nb, a, dim3(cdiv(n_cols, tw), 1, 1), stream);
   }
   if (scratch_elems < (uint64_t)n_cols * n || !d_scratch) return fail(WG_ERR_NOMEM, "interpolate scratch too small");
@@ -260,6 +296,7 @@ static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, u
   typename Tables<F>::Two tm;
   WG_TRY(tb.get_tm(log_n, true, &tm));
   {  // pass A: for each k2, transform over k1 (stride K2); Y[mA*K2 + k2] *= n^-1 w_n^(-mA*k2)
+    ProfScope ps(PH_INTERP_A, stream);
     PassArgs<F> a = blank_args<F>();
     a.in = d_in;
     a.out = d_scratch;
@@ -278,6 +315,7 @@ static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, u
     WG_TRY(launch_pass<F>(0, true, na, a, dim3(cdiv(K2, tw), n_cols, 1), stream));
   }
   {  // pass B: for each mA, transform over k2 (contiguous); c[mA + K1*mB]
+    ProfScope ps(PH_INTERP_B, stream);
     PassArgs<F> a = blank_args<F>();
     a.in = d_scratch;
     a.out = d_out;
@@ -342,6 +380,7 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
     a.pm_lb = pm.lb;
     a.pm_mask = (uint32_t)(n - 1);
     const int tw = 1 << pass_log_tw<F>(nb);
+    ProfScope ps(PH_LDE_B, stream);
     return launch_pass<F>(1, false, nb, a, dim3(cdiv(row_width, tw), 1, B), stream);
   }
   const uint64_t N1 = (uint64_t)1 << na, N2 = (uint64_t)1 << nb;
@@ -392,6 +431,7 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
       a.tm_mask = (uint32_t)(n - 1);
       a.tm_w = 1;
       const int tw = 1 << pass_log_tw<F>(na);
+      ProfScope ps(PH_LDE_A, stream);
       WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw), nc_in, B), stream));
     }
     {
@@ -411,6 +451,7 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
       a.nw_out = nc_out;
       WG_TRY(tb.get_tws(nb, false, &a.tws));
       const int tw = 1 << pass_log_tw<F>(nb);
+      ProfScope ps(PH_LDE_B, stream);
       WG_TRY(launch_pass<F>(1, false, nb, a, dim3(cdiv(nc_out, tw), (unsigned)N1, B), stream));
     }
   }
@@ -440,6 +481,7 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
   if (off * 8 > (1u << 22)) return fail(WG_ERR_UNSUPPORTED, "rows longer than 4 MiB");
   a.unit_off[n_traces] = (uint32_t)off;
   const unsigned blocks = cdiv(rows, 32 * HASH_WARPS);
+  ProfScope ps(PH_HASH, stream);
   if (hash == WG_HASH_BLAKE3_256)
     hash_rows_kernel<F, HASH_BLAKE3_256><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
   else
@@ -453,6 +495,7 @@ template <int HASH>
 static int merkle_dev_t(const uint8_t* d_leaves, uint64_t n_leaves, uint8_t* d_nodes, cudaStream_t stream) {
   uint4* nodes = reinterpret_cast<uint4*>(d_nodes);
   uint64_t n = n_leaves / 2;
+  ProfScope ps(PH_MERKLE, stream);
   merkle_level_kernel<HASH><<<cdiv(n, 256), 256, 0, stream>>>(reinterpret_cast<const uint4*>(d_leaves), nodes + 2 * n, n);
   CUDA_TRY(cudaGetLastError());
   g_launches++;
@@ -724,6 +767,30 @@ int wg_shutdown(void) { return WG_OK; }  // tables live for the process lifetime
 
 const char* wg_last_error(void) { return g_last_error.c_str(); }
 uint64_t wg_launch_count(void) { return g_launches.load(); }
+
+int wg_profile_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_prof_on = on != 0;
+  return WG_OK;
+}
+int wg_profile_read(float* ms_out, uint32_t* count_out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (int i = 0; i < PH_COUNT; i++) {
+    ms_out[i] = 0.f;
+    count_out[i] = 0;
+  }
+  for (auto& r : g_prof) {
+    CUDA_TRY(cudaEventSynchronize(r.b));
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r.a, r.b));
+    ms_out[r.phase] += ms;
+    count_out[r.phase]++;
+    g_prof_pool.push_back(r.a);
+    g_prof_pool.push_back(r.b);
+  }
+  g_prof.clear();
+  return WG_OK;
+}
 
 int wg_get_twiddles(int field, uint64_t n, int inverse, void* out) {
   if (!out) return fail(WG_ERR_ARG, "null output");
