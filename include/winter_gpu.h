@@ -55,6 +55,10 @@ uint64_t wg_launch_count(void);
 int wg_profile_enable(int on);
 int wg_profile_read(float* ms_out, uint32_t* count_out);
 
+/* Test probe: out[i] = op(a[i], b[i]) computed by the device field code (op 0 add, 1 sub, 2 mul in the internal
+ * representation, 16+i / 32+i multiply by the order-16 root to the +i / -i, 48 f64 as_int). Host buffers. */
+int wg_debug_field_op(int field, int op, const void* a, const void* b, void* out, uint32_t n);
+
 /* ---- host-buffer entry points (H2D + kernels + D2H inside) ------------------------------------------- */
 
 /* fft::get_twiddles / get_inv_twiddles (math/src/fft/mod.rs:466-482,505-522): n/2 elements, bit-reversed,

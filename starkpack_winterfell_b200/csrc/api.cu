@@ -530,13 +530,7 @@ __global__ void twiddles_kernel(typename F::T* out, uint32_t n, int log_half, in
   const uint32_t e = inverse ? ((n - i) & (n - 1)) : i;
   typename F::T v = table2<F>(lo, hi, lb, e);
   const uint32_t j = log_half == 0 ? 0 : (__brev(i) >> (32 - log_half));
-  if (F::kFieldId == 0) {
-    uint64_t w;
-    memcpy(&w, &v, 8);
-    w = Gl64::to_mont(w);
-    memcpy(&v, &w, 8);
-  }
-  out[j] = v;
+  out[j] = v;  // tables already hold the internal representation
 }
 
 template <class F>
@@ -551,6 +545,65 @@ static int get_twiddles_dev(uint64_t n, bool inverse, typename F::T* d_out, cuda
   return WG_OK;
 }
 
+struct DevBufFwd {
+  void* p = nullptr;
+  ~DevBufFwd() {
+    if (p) cudaFree(p);
+  }
+  int alloc(size_t bytes) {
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+    }
+    return WG_OK;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------ device arithmetic probe
+// Element-wise field ops on the device (tests/test_gpu_parity.py checks them against Python big ints):
+// op 0 add, 1 sub, 2 mul, 16+i mul_root16<false>(a, i), 32+i mul_root16<true>(a, i), 48 as_int (f64 only)
+template <class F>
+__global__ void field_op_kernel(int op, const typename F::T* a, const typename F::T* b, typename F::T* out, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  typename F::T x = a[i], y = b[i], r = x;
+  if (op == 0) r = F::add(x, y);
+  else if (op == 1) r = F::sub(x, y);
+  else if (op == 2) r = F::mul(x, y);
+  else if (op >= 16 && op < 32) {
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if (op - 16 == k) r = F::template mul_root16<false>(x, k);
+  } else if (op >= 32 && op < 48) {
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if (op - 32 == k) r = F::template mul_root16<true>(x, k);
+  } else if (op == 48) {
+    if (F::kFieldId == 0) {
+      uint64_t w;
+      memcpy(&w, &x, 8);
+      w = Gl64::as_int(w);
+      memcpy(&r, &w, 8);
+    }
+  }
+  out[i] = r;
+}
+template <class F>
+static int h_field_op(int op, const void* a, const void* b, void* out, uint32_t n) {
+  typedef typename F::T T;
+  DevBufFwd da, db, dout;
+  WG_TRY(da.alloc(n * sizeof(T)));
+  WG_TRY(db.alloc(n * sizeof(T)));
+  WG_TRY(dout.alloc(n * sizeof(T)));
+  CUDA_TRY(cudaMemcpy(da.p, a, n * sizeof(T), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(db.p, b, n * sizeof(T), cudaMemcpyHostToDevice));
+  field_op_kernel<F><<<cdiv(n, 128), 128>>>(op, (const T*)da.p, (const T*)db.p, (T*)dout.p, n);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(out, dout.p, n * sizeof(T), cudaMemcpyDeviceToHost));
+  return WG_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ whole commit
 template <class F>
 static typename F::T generator() {
@@ -558,14 +611,8 @@ static typename F::T generator() {
 }
 template <class F>
 static typename F::T offset_from_internal(const void* p) {
-  typename F::T v;
+  typename F::T v;  // kernels compute on the reference's internal representation directly
   memcpy(&v, p, sizeof v);
-  if (F::kFieldId == 0) {
-    uint64_t w;
-    memcpy(&w, &v, 8);
-    w = Gl64::as_int(w);  // Montgomery word -> plain value
-    memcpy(&v, &w, 8);
-  }
   return v;
 }
 
@@ -767,6 +814,12 @@ int wg_shutdown(void) { return WG_OK; }  // tables live for the process lifetime
 
 const char* wg_last_error(void) { return g_last_error.c_str(); }
 uint64_t wg_launch_count(void) { return g_launches.load(); }
+
+int wg_debug_field_op(int field, int op, const void* a, const void* b, void* out, uint32_t n) {
+  if (!a || !b || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_field_op<Gl64>(op, a, b, out, n), h_field_op<F128>(op, a, b, out, n));
+}
 
 int wg_profile_enable(int on) {
   std::lock_guard<std::mutex> lk(g_mu);

@@ -33,95 +33,128 @@ WG_HD void mul64wide(uint64_t a, uint64_t b, uint64_t& hi, uint64_t& lo) {
 }
 
 // ------------------------------------------------------------------------------------------------ Gl64
+// Elements are MONTGOMERY WORDS x*2^64 mod p in [0,p), exactly the reference's BaseElement(u64); mul is the
+// reference's Montgomery multiplication (f64/mod.rs:356-361 with mont_red_cst :651-661), so twiddle tables are
+// Montgomery words too. On the device add/sub/mont_red are written as 32-bit carry chains in PTX: the
+// straightforward C forms compile to 10 / 10 / 33 SASS instructions, these to 8 / 5 / ~17, and the product's
+// four IMAD.WIDE run on the FMA pipe while the carry chains run on the ALU pipe.
 struct Gl64 {
   typedef uint64_t T;
   static constexpr int kFieldId = 0;
   static constexpr int kElemBytes = 8;
   static constexpr int kTwoAdicity = 32;                         // f64/mod.rs:252
   static constexpr uint64_t P = 0xFFFFFFFF00000001ULL;            // f64/mod.rs:37
-  static constexpr uint64_t EPS = 0xFFFFFFFFULL;                  // 2^64 mod p
+  static constexpr uint64_t EPS = 0xFFFFFFFFULL;                  // 2^64 mod p (= Montgomery form of 1)
   static constexpr uint64_t ROOT_CANON = 7277203076849721926ULL;  // f64/mod.rs:264 (order 2^32)
   static constexpr uint64_t GENERATOR_CANON = 7;                  // f64/mod.rs:248
 
   static WG_HD T zero() { return 0; }
-  static WG_HD T one() { return 1; }
-  static WG_HD T from_u64(uint64_t v) { return v >= P ? v - P : v; }
+  static WG_HD T one() { return EPS; }
   static WG_HD bool is_zero(T a) { return a == 0; }
 
   static WG_HD T add(T a, T b) {
+#if defined(__CUDA_ARCH__)
+    // a - (p - b), then + p on borrow (the reference's formulation, f64/mod.rs:314-324)
+    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), d0, d1;
+    asm("{\n\t.reg .u32 m, t0, t1;\n\t"
+        "sub.cc.u32 t0, 1, %4;\n\tsubc.u32 t1, 0xFFFFFFFF, %5;\n\t"
+        "sub.cc.u32 %0, %2, t0;\n\tsubc.cc.u32 %1, %3, t1;\n\tsubc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(d0), "=&r"(d1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((uint64_t)d1 << 32) | d0;
+#else
     uint64_t s = a + b;
-    // a,b < p: overflow past 2^64 or landing in [p, 2^64) both mean "subtract p" (== add EPS mod 2^64)
     if (s < a || s >= P) s += EPS;
     return s;
+#endif
   }
   static WG_HD T sub(T a, T b) {
+#if defined(__CUDA_ARCH__)
+    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), d0, d1;
+    asm("{\n\t.reg .u32 m;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\tsubc.cc.u32 %1, %3, %5;\n\tsubc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(d0), "=&r"(d1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+    return ((uint64_t)d1 << 32) | d0;
+#else
     uint64_t d = a - b;
     if (a < b) d -= EPS;  // + p
     return d;
+#endif
   }
   static WG_HD T neg(T a) { return a ? P - a : 0; }
 
-  // (hi*2^64 + lo) mod p, using 2^64 = 2^32 - 1 and 2^96 = -1
-  static WG_HD T reduce128(uint64_t hi, uint64_t lo) {
-    uint64_t hh = hi >> 32, hl = hi & EPS;
-    uint64_t t0 = lo - hh;
-    if (lo < hh) t0 -= EPS;
-    uint64_t t1 = hl * EPS;  // (hl << 32) - hl, < 2^64
-    uint64_t r = t0 + t1;
-    if (r < t0) r += EPS;
-    if (r >= P) r -= P;
-    return r;
-  }
-  static WG_HD T mul(T a, T b) {
-    uint64_t hi, lo;
-    mul64wide(a, b, hi, lo);
-    return reduce128(hi, lo);
-  }
-  // x * 2^k mod p for 0 <= k < 192 (2^96 = -1, 2^192 = 1). k is a compile-time constant at every call site.
-  static WG_HD T mul_pow2(T x, int k) {
-    bool negate = false;
-    if (k >= 96) {
-      k -= 96;
-      negate = true;
-    }
-    T r;
-    if (k == 0) {
-      r = x;
-    } else if (k < 64) {
-      r = reduce128(x >> (64 - k), x << k);
-    } else if (k == 64) {
-      r = reduce128(x, 0);
-    } else {
-      // x*2^k = w4*2^128 + hi*2^64, w4 = bits above 2^128; 2^128 = -2^32
-      int s = k - 64;
-      uint64_t hi = x << s, w4 = x >> (64 - s);  // w4 < 2^32
-      r = sub(reduce128(hi, 0), w4 << 32);       // w4<<32 <= 2^64 - 2^32 < p
-    }
-    return negate ? neg(r) : r;
-  }
-
-  // reference Montgomery reduction x*2^-64 mod p (f64/mod.rs:651-661), x = xh*2^64 + xl
+  // reference Montgomery reduction x*2^-64 mod p (f64/mod.rs:651-661), x = xh*2^64 + xl < p*2^64; result in [0,p).
+  // Regrouped as r = (xh + a1 + e) - (a1:l0) with a1 = (l1 + l0) mod 2^32, e its carry (xh + 2^32 cannot overflow
+  // for xh < p - 2^32, which holds for products of reduced elements).
   static WG_HD uint64_t mont_red(uint64_t xh, uint64_t xl) {
+#if defined(__CUDA_ARCH__)
+    uint32_t l0 = (uint32_t)xl, l1 = (uint32_t)(xl >> 32), h0 = (uint32_t)xh, h1 = (uint32_t)(xh >> 32), r0, r1;
+    asm("{\n\t.reg .u32 a1, s0, s1, m;\n\t"
+        "add.cc.u32 a1, %3, %2;\n\t"
+        "addc.cc.u32 s0, %4, a1;\n\taddc.u32 s1, %5, 0;\n\t"
+        "sub.cc.u32 %0, s0, %2;\n\tsubc.cc.u32 %1, s1, a1;\n\tsubc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(l0), "r"(l1), "r"(h0), "r"(h1));
+    return ((uint64_t)r1 << 32) | r0;
+#else
     uint64_t a = xl + (xl << 32);
     uint64_t e = a < xl ? 1 : 0;
     uint64_t b = a - (a >> 32) - e;
     uint64_t r = xh - b;
     if (xh < b) r -= EPS;
     return r;
+#endif
+  }
+  // Montgomery product a*b*2^-64 mod p of two words in [0,p)
+  static WG_HD T mul(T a, T b) {
+#if defined(__CUDA_ARCH__)
+    const uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
+    const uint64_t t = (uint64_t)a0 * b0, u = (uint64_t)a1 * b1;
+    const uint64_t v = (uint64_t)a0 * b1 + (t >> 32);
+    const uint64_t w = (uint64_t)a1 * b0 + (uint32_t)v;
+    return mont_red(u + (v >> 32) + (w >> 32), (w << 32) | (uint32_t)t);
+#else
+    uint64_t hi, lo;
+    mul64wide(a, b, hi, lo);
+    return mont_red(hi, lo);
+#endif
+  }
+
+  // (hi*2^64 + lo) mod p, plain reduction (2^64 = 2^32 - 1, 2^96 = -1); host-side table building only
+  static WG_HD T reduce128(uint64_t hi, uint64_t lo) {
+    uint64_t hh = hi >> 32, hl = hi & EPS;
+    uint64_t t0 = lo - hh;
+    if (lo < hh) t0 -= EPS;
+    uint64_t t1 = hl * EPS;
+    uint64_t r = t0 + t1;
+    if (r < t0) r += EPS;
+    if (r >= P) r -= P;
+    return r;
   }
   // internal word -> canonical integer (f64/mod.rs:275-282). Input any u64, output in [0,p).
   static WG_HD uint64_t as_int(uint64_t w) { return mont_red(0, w); }
   // canonical integer -> internal Montgomery word (f64/mod.rs:57-59): v * 2^64 mod p
   static WG_HD uint64_t to_mont(uint64_t v) { return reduce128(v >= P ? v - P : v, 0); }
+  static WG_HD T from_canon(uint64_t v) { return to_mont(v); }
+  static WG_HD T from_u64(uint64_t v) { return to_mont(v); }
 
-  // w16^idx (forward) or w16^-idx (inverse) where w16 = 2^12 is the order-16 root matching ROOT_CANON
-  // (ROOT^(2^26) = 8, so w64 = 2^3).
+  // 2^e mod p for 0 <= e < 192 (2^96 = -1), canonical
+  static WG_HD constexpr uint64_t pow2_mod(int e) {
+    return e >= 96 ? P - pow2_mod(e - 96) : (e < 64 ? (1ULL << e) : ((1ULL << (e - 32)) - (1ULL << (e - 64))));
+  }
+  // x * w16^(+-idx), w16 = 2^12 (ROOT^(2^26) = 8 so the order-16 root is a power of two).
+  // Multiplying a Montgomery word by the plain constant 2^k is a Montgomery product with 2^(k+64).
   template <bool INV>
   static WG_HD T mul_root16(T x, int idx) {
     idx &= 15;
-    int k = 12 * idx;
-    if (INV && idx) k = 192 - k;
-    return mul_pow2(x, k);
+    if (idx == 0) return x;
+    if (idx == 8) return neg(x);
+    const int k = INV ? 192 - 12 * idx : 12 * idx;
+    return mul(x, pow2_mod((k + 64) % 192));
   }
 };
 
@@ -165,6 +198,7 @@ struct F128 {
   static WG_HD T zero() { return T{0, 0}; }
   static WG_HD T one() { return T{1, 0}; }
   static WG_HD T from_u64(uint64_t v) { return T{v, 0}; }
+  static WG_HD T from_canon(uint64_t v) { return T{v, 0}; }
   static WG_HD bool is_zero(T a) { return (a.lo | a.hi) == 0; }
   static WG_HD T canon(T a) { return u128_lt(a, modulus()) ? a : u128_sub(a, modulus()); }
 
@@ -297,7 +331,7 @@ template <class F>
 inline typename F::T f_root_of_unity(int log_n);
 template <>
 inline uint64_t f_root_of_unity<Gl64>(int log_n) {
-  uint64_t r = Gl64::ROOT_CANON;
+  uint64_t r = Gl64::to_mont(Gl64::ROOT_CANON);
   for (int i = 0; i < Gl64::kTwoAdicity - log_n; i++) r = Gl64::mul(r, r);
   return r;
 }

@@ -10,7 +10,7 @@ uint64_t wgt_gl(int op, uint64_t a, uint64_t b) {
     case 0: return Gl64::add(a, b);
     case 1: return Gl64::sub(a, b);
     case 2: return Gl64::mul(a, b);
-    case 3: return Gl64::mul_pow2(a, (int)b);
+    case 3: return Gl64::pow2_mod((int)b);
     case 4: return Gl64::as_int(a);
     case 5: return Gl64::to_mont(a);
     case 6: return Gl64::neg(a);

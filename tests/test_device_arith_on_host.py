@@ -35,38 +35,41 @@ def L():
 EDGE64 = [0, 1, 2, P - 1, P - 2, 2**32 - 1, 2**32, 2**32 + 1, 2**63, P - 2**32, 0xFFFFFFFF00000000]
 
 
+RINV = pow(2**64, -1, P)
+
+
 def test_gl64_add_sub_mul(L):
+    """words are Montgomery words; mul is the reference's Montgomery product (f64/mod.rs:356-361,651-661)."""
     rnd = random.Random(1)
     vals = EDGE64 + [rnd.randrange(P) for _ in range(1500)]
     for a in vals:
         for b in rnd.sample(vals, 4) + EDGE64:
             assert L.wgt_gl(0, a, b) == (a + b) % P
             assert L.wgt_gl(1, a, b) == (a - b) % P
-            assert L.wgt_gl(2, a, b) == (a * b) % P
+            assert L.wgt_gl(2, a, b) == a * b * RINV % P
         assert L.wgt_gl(6, a, 0) == (-a) % P
 
 
-def test_gl64_mul_pow2_and_root16(L):
+def test_gl64_pow2_and_root16(L):
     rnd = random.Random(2)
     w16 = pow(ROOT64, 1 << 28, P)
     assert w16 == 2**12  # the order-64 root is 8 (f64/mod.rs:254-264)
+    for k in range(192):
+        assert L.wgt_gl(3, 0, k) == pow(2, k, P)
     for a in EDGE64 + [rnd.randrange(P) for _ in range(300)]:
-        for k in range(192):
-            assert L.wgt_gl(3, a, k) == a * pow(2, k, P) % P
-        for i in range(16):
+        for i in range(16):  # linear map on the stored word, so it holds for Montgomery words as well
             assert L.wgt_gl(7, a, i) == a * pow(w16, i, P) % P
             assert L.wgt_gl(8, a, i) == a * pow(w16, -i, P) % P
 
 
 def test_gl64_mont_conversions_and_roots(L):
     rnd = random.Random(3)
-    rinv = pow(2**64, -1, P)
     for w in EDGE64 + [M64, P, P + 1] + [rnd.randrange(2**64) for _ in range(3000)]:
-        assert L.wgt_gl(4, w, 0) == w * rinv % P  # as_int accepts any u64 (f64/mod.rs:275-282)
+        assert L.wgt_gl(4, w, 0) == w * RINV % P  # as_int accepts any u64 (f64/mod.rs:275-282)
         assert L.wgt_gl(5, w, 0) == (w % P) * 2**64 % P
-    for ln in range(33):  # math/src/field/traits.rs:254-263
-        assert L.wgt_gl(9, ln, 0) == pow(ROOT64, 1 << (32 - ln), P)
-    assert L.wgt_gl(10, 12345, 0) == pow(12345, -1, P)
+    for ln in range(33):  # math/src/field/traits.rs:254-263, returned as a Montgomery word
+        assert L.wgt_gl(9, ln, 0) == pow(ROOT64, 1 << (32 - ln), P) * 2**64 % P
+    assert L.wgt_gl(10, 12345 * 2**64 % P, 0) == pow(12345, -1, P) * 2**64 % P
 
 
 def _f128(L, op, a, b):

@@ -36,6 +36,54 @@ def rand_cols(field, seed, cols, n):
     return fx.synth_f64(seed, cols, n) if field == F64 else fx.synth_f128(seed, cols, n)
 
 
+def _field_op(wg, field, op, a, b):
+    import ctypes as C
+
+    from starkpack_winterfell_b200._lib import check, lib
+
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    b = np.ascontiguousarray(b, dtype=np.uint64)
+    out = np.empty_like(a)
+    check(lib().wg_debug_field_op(field, op, C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data), C.c_void_p(out.ctypes.data), a.shape[0]))
+    return out
+
+
+def test_device_field_ops_f64(wg):
+    """the PTX carry-chain add/sub/Montgomery product the kernels run, against Python big ints
+    (math/src/field/f64/tests.rs:17-250 style: edge values + random)."""
+    rng = np.random.default_rng(11)
+    edge = [0, 1, 2, P64 - 1, P64 - 2, 2**32 - 1, 2**32, 2**32 + 1, 2**63, P64 - 2**32, 0xFFFFFFFF00000000]
+    a = np.array(edge * len(edge) + [int(x) % P64 for x in rng.integers(0, 2**64, 4000, dtype=np.uint64)], dtype=np.uint64)
+    b = np.array([e for e in edge for _ in edge] + [int(x) % P64 for x in rng.integers(0, 2**64, 4000, dtype=np.uint64)], dtype=np.uint64)
+    rinv = pow(2**64, -1, P64)
+    A, Bv = [int(x) for x in a], [int(x) for x in b]
+    assert [int(x) for x in _field_op(wg, F64, 0, a, b)] == [(x + y) % P64 for x, y in zip(A, Bv)]
+    assert [int(x) for x in _field_op(wg, F64, 1, a, b)] == [(x - y) % P64 for x, y in zip(A, Bv)]
+    assert [int(x) for x in _field_op(wg, F64, 2, a, b)] == [x * y * rinv % P64 for x, y in zip(A, Bv)]
+    for i in range(16):
+        assert [int(x) for x in _field_op(wg, F64, 16 + i, a, b)] == [x * pow(2, 12 * i, P64) % P64 for x in A], i
+        assert [int(x) for x in _field_op(wg, F64, 32 + i, a, b)] == [x * pow(2, -12 * i, P64) % P64 for x in A], i
+    w = rng.integers(0, 2**64, 4000, dtype=np.uint64)
+    assert [int(x) for x in _field_op(wg, F64, 48, w, w)] == [int(x) * rinv % P64 for x in w]
+
+
+def test_device_field_ops_f128(wg):
+    rng = np.random.default_rng(12)
+    q = fx.P128
+    vals = [0, 1, q - 1, q - 2, 2**64 - 1, 2**64, 2**127, q - 2**64] + [int.from_bytes(rng.bytes(16), "little") % q for _ in range(3000)]
+    a = np.array([(v & fx.MASK, v >> 64) for v in vals], dtype=np.uint64)
+    bv = vals[::-1]
+    b = np.array([(v & fx.MASK, v >> 64) for v in bv], dtype=np.uint64)
+    un = lambda r: [int(x[0]) | (int(x[1]) << 64) for x in r]
+    assert un(_field_op(wg, F128, 0, a, b)) == [(x + y) % q for x, y in zip(vals, bv)]
+    assert un(_field_op(wg, F128, 1, a, b)) == [(x - y) % q for x, y in zip(vals, bv)]
+    assert un(_field_op(wg, F128, 2, a, b)) == [(x * y) % q for x, y in zip(vals, bv)]
+    w16 = pow(23953097886125630542083529559205016746, 1 << 36, q)
+    for i in range(16):
+        assert un(_field_op(wg, F128, 16 + i, a, b)) == [x * pow(w16, i, q) % q for x in vals], i
+        assert un(_field_op(wg, F128, 32 + i, a, b)) == [x * pow(w16, -i, q) % q for x in vals], i
+
+
 SIZES = [2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 1 << 14, 1 << 15, 1 << 17]
 
 
