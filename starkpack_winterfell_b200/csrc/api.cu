@@ -94,17 +94,29 @@ struct Tables {
     return inv ? f_inv<F>(r) : r;
   }
 
+  // in-block twiddles in the per-step [j][m_rest] layout of PassCfg::tws_off (ntt.cuh)
   int get_tws(int log_s, bool inv, const T** out) {
     std::lock_guard<std::mutex> lk(mu);
     auto key = std::make_pair(log_s, (int)inv);
     auto it = tws.find(key);
     if (it == tws.end()) {
-      std::vector<T> h((size_t)1 << log_s);
+      const int maxlr = FieldCfg<F>::MAXLR;
+      const int nsteps = (log_s + maxlr - 1) / maxlr;
+      std::vector<T> pw((size_t)1 << log_s);  // w_S^e
       T w = root(log_s, inv), acc = F::one();
-      for (auto& x : h) {
+      for (auto& x : pw) {
         x = acc;
         acc = F::mul(acc, w);
       }
+      std::vector<T> h;
+      int logpp = log_s;
+      for (int u = 0; u + 1 < nsteps; u++) {
+        const int lr = maxlr, logp = logpp - lr;
+        for (int j = 0; j < (1 << lr); j++)
+          for (int m = 0; m < (1 << logp); m++) h.push_back(pw[((size_t)m * j) << (log_s - logpp)]);
+        logpp = logp;
+      }
+      if (h.empty()) h.push_back(F::one());
       T* d;
       WG_TRY(upload(h, &d));
       it = tws.emplace(key, d).first;

@@ -154,7 +154,11 @@ struct Gl64 {
 
   // 2^e mod p for 0 <= e < 192 (2^96 = -1), canonical
   static WG_HD constexpr uint64_t pow2_mod(int e) {
-    return e >= 96 ? P - pow2_mod(e - 96) : (e < 64 ? (1ULL << e) : ((1ULL << (e - 32)) - (1ULL << (e - 64))));
+    // not recursive on purpose: a recursive constexpr is not inlined in device code and ends up as a run-time CALL
+    const bool negate = e >= 96;
+    const int f = negate ? e - 96 : e;
+    const uint64_t v = f < 64 ? (1ULL << (f & 63)) : ((1ULL << ((f - 32) & 63)) - (1ULL << ((f - 64) & 63)));
+    return negate ? P - v : v;
   }
   // x * w16^(+-idx), w16 = 2^12 (ROOT^(2^26) = 8 so the order-16 root is a power of two).
   // Multiplying a Montgomery word by the plain constant 2^k is a Montgomery product with 2^(k+64).

@@ -35,7 +35,8 @@ struct PassArgs {
   long long out_ystride, out_zstride, out_wstride, out_jstride;
   uint32_t nw_in;   // problems with wg >= nw_in read as zero
   uint32_t nw_out;  // problems with wg >= nw_out are not written
-  // in-block twiddles w_S^(+-e), e < S
+  // in-block twiddles, one sub-table per register step u < NSTEPS-1 laid out [j][m_rest]:
+  // tws[off_u + j*P_u + m] = w_{P_{u-1}}^(+-m*j)  (lanes walk m, so shared-memory reads are conflict-free)
   const T* tws;
   // optional pre-multiplication x[s] *= PM^(s*pm_s + wg*pm_w)  (two-level table, per-z tables)
   const T* pm_lo;
@@ -89,10 +90,17 @@ template <class F>
 struct FieldCfg;
 template <>
 struct FieldCfg<Gl64> {
-  static constexpr int MAXLR = 4;      // radix-16 register butterflies
-  static constexpr int LOG_TILE = 14;  // S*TW <= 2^14 elements (128 KB)
+  static constexpr int MAXLR = 4;  // radix-16 register butterflies
+#ifndef WG_GL_LOG_TILE
+#define WG_GL_LOG_TILE 13
+#endif
+#ifndef WG_GL_MINB
+#define WG_GL_MINB 2
+#endif
+  static constexpr int LOG_TILE = WG_GL_LOG_TILE;  // S*TW <= 2^LOG_TILE elements (64 KB at 13)
   static constexpr int MAX_LOG_TW = 3;
   static constexpr int PAD_LOG = 3;  // pad unit: 8 elements = 64 B
+  static constexpr int MIN_BLOCKS = WG_GL_MINB;  // resident 512-thread blocks per SM the kernels are compiled for
 };
 template <>
 struct FieldCfg<F128> {
@@ -100,6 +108,7 @@ struct FieldCfg<F128> {
   static constexpr int LOG_TILE = 13;
   static constexpr int MAX_LOG_TW = 2;
   static constexpr int PAD_LOG = 2;  // 4 elements = 64 B
+  static constexpr int MIN_BLOCKS = 1;
 };
 
 template <class F, int LOG_S, int LAYOUT>
@@ -134,7 +143,13 @@ struct PassCfg {
   }
   static constexpr int TILE_ELEMS =
       NSTEPS == 1 ? 0 : (LAYOUT == 0 ? (S * TW + (((S * TW) >> PAD_SHIFT) << FC::PAD_LOG)) : TW * SP);
-  static constexpr int TWS_ELEMS = NSTEPS == 1 ? 0 : S;
+  // offset of step u's twiddle sub-table; sub-table u has R_u * P_u = 2^(logp(u) + lr(u)) entries
+  static constexpr __host__ __device__ int tws_off(int u) {
+    int o = 0;
+    for (int v = 0; v < u; v++) o += 1 << (logp(v) + lr(v));
+    return o;
+  }
+  static constexpr int TWS_ELEMS = NSTEPS == 1 ? 0 : tws_off(NSTEPS - 1);
   static constexpr size_t SMEM_BYTES = (size_t)(TILE_ELEMS + TWS_ELEMS) * sizeof(typename F::T);
 };
 
@@ -201,11 +216,11 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
     radix_ntt<F, LR, INV>(a);
 
     if (!LAST) {
-      // twiddle w_{2^LOGPP}^(m_rest*j) = w_S^(m_rest*j << (LOG_S-LOGPP)); then scatter digit j
+      // twiddle w_{2^LOGPP}^(m_rest*j) from this step's [j][m_rest] sub-table; then scatter digit j
 #pragma unroll
       for (int j = 0; j < R; j++) {
         T v = a[j];
-        if (j > 0) v = F::mul(v, tws[(m_rest * j) << (LOG_S - LOGPP)]);
+        if (j > 0) v = F::mul(v, tws[C::tws_off(U) + (j << LOGP) + m_rest]);
         tile[C::phys(s0 + (j << LOGP), w)] = v;
       }
     } else {
@@ -256,14 +271,14 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
 }
 
 template <class F, int LOG_S, int LAYOUT, bool INV>
-__global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT) ntt_pass_kernel(const PassArgs<F> A) {
+__global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MIN_BLOCKS) ntt_pass_kernel(const PassArgs<F> A) {
   typedef typename F::T T;
   typedef PassCfg<F, LOG_S, LAYOUT> C;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* tile = reinterpret_cast<T*>(smem_raw);
   T* tws = tile + C::TILE_ELEMS;
   if (C::NSTEPS > 1) {
-    for (int i = threadIdx.x; i < C::S; i += C::NT) tws[i] = A.tws[i];
+    for (int i = threadIdx.x; i < C::TWS_ELEMS; i += C::NT) tws[i] = A.tws[i];
   }
   const uint32_t w0 = blockIdx.x * C::TW;
   const long long in_base = (long long)blockIdx.y * A.in_ystride + (long long)blockIdx.z * A.in_zstride;
