@@ -150,3 +150,17 @@ def commit_trace(field, hash_id, traces, blowup, want=("polys", "lde", "leaves",
     if rc:
         raise ValueError(f"or_commit_trace rc={rc}")
     return dict(polys=polys, lde=ldes, leaves=leaves, nodes=nodes, root=root)
+
+
+def hash_comb_rows(field, hash_id, mats, elems):
+    """commit_to_comb_rows leaves (row_matrix.rs:204-238) over several row-major matrices [rows, rw_i(,2)]."""
+    mats = [np.ascontiguousarray(m, dtype=np.uint64) for m in mats]
+    rows = mats[0].shape[0]
+    k = len(mats)
+    ptrs = (C.c_void_p * k)(*[m.ctypes.data for m in mats])
+    rws = (C.c_uint64 * k)(*[m.shape[1] for m in mats])
+    els = (C.c_uint64 * k)(*elems)
+    leaves = np.empty((rows, 32), dtype=np.uint8)
+    rc = lib().or_hash_comb_rows(field, hash_id, C.c_uint32(k), ptrs, rws, els, C.c_uint64(rows), _p(leaves))
+    assert rc == 0
+    return leaves

@@ -1,0 +1,165 @@
+"""One Merkle tree over an LDE that is sharded by columns across G GPUs (BASELINE configs[3], [4]).
+
+The reference has no distributed code; its `commit_to_comb_rows` (prover/src/matrix/row_matrix.rs:204-238) needs whole
+rows (all columns of all aggregated traces) to form a leaf. Interpolation and LDE are independent per column, so:
+
+  1. every rank interpolates + LDEs ITS columns (contiguous block of the global column list: trace 0 col 0, ...,
+     trace T-1 col last) into a local row-major matrix [L, rw_g];
+  2. ONE all-to-all (torch.distributed, NCCL over NVLink) turns column shards into row blocks: rank g receives rows
+     [g*L/G, (g+1)*L/G) of every shard — a contiguous slice on the sender;
+  3. rank g hashes its rows (the leaf kernel concatenates the G received matrices, skipping pad columns, so the bytes
+     hashed are exactly the reference's) and builds the subtree over its L/G leaves;
+  4. the G subtree roots are all-gathered and the top log2(G) levels are computed (redundantly on every rank; the
+     result on rank 0 is the commitment). `gather_nodes()` stitches the reference's heap-layout node array.
+
+One process per GPU. All compute goes through a backend with four methods; the product backend is the C ABI
+(`DeviceBackend`); tests/ substitutes a CPU checker backend to exercise the partition / exchange / stitching logic under
+gloo without a GPU.
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import ELEM_BYTES, check, lib
+
+
+def split_columns(total_cols, world):
+    """contiguous, as even as possible: first (total % world) ranks get one more. -> list of (start, count)."""
+    base, extra = divmod(total_cols, world)
+    out, s = [], 0
+    for g in range(world):
+        c = base + (1 if g < extra else 0)
+        out.append((s, c))
+        s += c
+    return out
+
+
+def stitch_nodes(local_nodes, top_nodes, world):
+    """local_nodes[g]: [L/G, 32] heap layout of rank g's subtree; top_nodes: [G, 32] heap layout of the tree over the G
+    subtree roots. Returns the global [L, 32] heap-layout array of crypto/src/merkle/mod.rs:350-374."""
+    lg = local_nodes[0].shape[0]
+    L = lg * world
+    out = torch.zeros((L, 32), dtype=torch.uint8)
+    out[1:world] = top_nodes[1:world].cpu() if world > 1 else out[1:world]
+    m = world
+    while m < L:
+        per = m // world  # nodes of this level owned by each rank: local level `per`
+        for g in range(world):
+            out[m + g * per: m + (g + 1) * per] = local_nodes[g][per: 2 * per].cpu()
+        m *= 2
+    return out
+
+
+class DeviceBackend:
+    """Compute through libwinter_gpu.so on the current CUDA device."""
+
+    def __init__(self, field, hash_id, device):
+        self.field, self.hash_id, self.device = field, hash_id, torch.device(device)
+        _lib.init(self.device.index or 0)
+        self.w = ELEM_BYTES[field] // 8
+        from .matrix import GENERATOR_INTERNAL
+
+        self._offset = GENERATOR_INTERNAL[field]
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def empty(self, shape, dtype=torch.int64):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def interpolate_lde(self, cols, n, blowup):
+        """cols: [c, n, w] int64 -> (polys [c, n, w], lde [n*blowup, rw, w])"""
+        c = cols.shape[0]
+        rw = (c + 7) // 8 * 8
+        polys = torch.empty_like(cols)
+        lde = self.empty((n * blowup, rw, self.w))
+        se = max(lib().wg_interpolate_scratch_elems(self.field, c, n), lib().wg_lde_scratch_elems(self.field, c, n, blowup))
+        scratch = self.empty((max(int(se), 1), self.w))
+        check(lib().wg_interpolate_columns_dev(self.field, C.c_void_p(cols.data_ptr()), c, n, C.c_void_p(polys.data_ptr()),
+                                               C.c_void_p(scratch.data_ptr()), int(se), self._stream()))
+        check(lib().wg_lde_dev(self.field, C.c_void_p(polys.data_ptr()), c, n, blowup, C.c_void_p(self._offset.ctypes.data),
+                               C.c_void_p(lde.data_ptr()), rw, C.c_void_p(scratch.data_ptr()), int(se), self._stream()))
+        return polys, lde
+
+    def hash_rows(self, mats, elems, rows):
+        """mats: list of [rows, rw_i, w] int64 row blocks; elems[i] real columns of block i -> leaves [rows, 32]"""
+        k = len(mats)
+        ptrs = (C.c_void_p * k)(*[m.data_ptr() for m in mats])
+        rws = (C.c_uint64 * k)(*[m.shape[1] for m in mats])
+        els = (C.c_uint64 * k)(*elems)
+        leaves = self.empty((rows, 32), torch.uint8)
+        check(lib().wg_hash_rows_dev(self.field, self.hash_id, k, ptrs, rws, els, rows, C.c_void_p(leaves.data_ptr()), self._stream()))
+        return leaves
+
+    def merkle(self, leaves):
+        nodes = self.empty((leaves.shape[0], 32), torch.uint8)
+        check(lib().wg_merkle_dev(self.hash_id, C.c_void_p(leaves.data_ptr()), leaves.shape[0], C.c_void_p(nodes.data_ptr()), self._stream()))
+        return nodes
+
+
+class DistributedCommitter:
+    def __init__(self, backend, n_rows, blowup, total_cols, group=None):
+        self.b, self.n, self.blowup, self.total_cols, self.group = backend, n_rows, blowup, total_cols, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert self.world & (self.world - 1) == 0, "number of ranks must be a power of two"
+        self.L = n_rows * blowup
+        assert self.L % self.world == 0 and self.L // self.world >= 2
+        self.shards = split_columns(total_cols, self.world)
+        assert all(c > 0 for _, c in self.shards), "more ranks than columns"
+        self.col_start, self.col_count = self.shards[self.rank]
+
+    def commit(self, local_cols):
+        """local_cols: [col_count, n, w] — this rank's block of the global column list. Returns the 32-byte root
+        (identical on every rank); keeps polys / lde shard / leaves / local nodes / top nodes as attributes."""
+        G, L = self.world, self.L
+        rows = L // G
+        assert local_cols.shape[0] == self.col_count
+        self.polys, self.lde = self.b.interpolate_lde(local_cols, self.n, self.blowup)
+        w = self.lde.shape[2]
+        rws = [(c + 7) // 8 * 8 for _, c in self.shards]
+        # --- the one exchange: column shards -> row blocks
+        send = self.lde.reshape(-1)
+        recv = self.b.empty((sum(rows * r * w for r in rws),))
+        in_splits = [rows * rws[self.rank] * w] * G
+        out_splits = [rows * r * w for r in rws]
+        if G > 1:
+            dist.all_to_all_single(recv, send, out_splits, in_splits, group=self.group)
+        else:
+            recv.copy_(send)
+        mats, off = [], 0
+        for r in rws:
+            mats.append(recv[off: off + rows * r * w].view(rows, r, w))
+            off += rows * r * w
+        self.row_block = mats
+        # --- leaves of my rows over ALL columns, my subtree
+        self.leaves = self.b.hash_rows(mats, [c for _, c in self.shards], rows)
+        self.local_nodes = self.b.merkle(self.leaves)
+        # --- top log2(G) levels over the G subtree roots
+        my_root = self.local_nodes[1].contiguous()
+        if G > 1:
+            roots = [torch.empty_like(my_root) for _ in range(G)]
+            dist.all_gather(roots, my_root, group=self.group)
+            self.top_nodes = self.b.merkle(torch.stack(roots).contiguous())
+            return bytes(self.top_nodes[1].cpu().numpy())
+        self.top_nodes = self.local_nodes[:1]
+        return bytes(my_root.cpu().numpy())
+
+    def gather_nodes(self):
+        """Global heap-layout node array on every rank (verification / handing the tree to a CPU prover)."""
+        G = self.world
+        if G == 1:
+            return self.local_nodes.cpu()
+        parts = [torch.empty_like(self.local_nodes) for _ in range(G)]
+        dist.all_gather(parts, self.local_nodes.contiguous(), group=self.group)
+        return stitch_nodes(parts, self.top_nodes, G)
+
+    def gather_leaves(self):
+        G = self.world
+        if G == 1:
+            return self.leaves.cpu()
+        parts = [torch.empty_like(self.leaves) for _ in range(G)]
+        dist.all_gather(parts, self.leaves.contiguous(), group=self.group)
+        return torch.cat([p.cpu() for p in parts])
