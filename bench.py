@@ -207,6 +207,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's version banner out of stdout: rank 0 prints ONE JSON line
         import torch.distributed as dist_mod
 
         dist_mod.init_process_group("nccl", device_id=dev)

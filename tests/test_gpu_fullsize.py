@@ -1,0 +1,110 @@
+"""BASELINE.json configs at FULL size on the GPU. Where the oracle finishes in seconds (configs 1, 3, 4: f128, 2^20
+rows) the whole result is compared; for config 2 (2^22 x 100 f64) size-independent properties are checked with
+independent tools (Python big-int Horner evaluation, the `blake3` module): polys evaluate back to the trace, LDE entries
+equal P_c(offset * g^k), leaves equal the hash of the canonical row bytes, Merkle paths verify against the root, pad
+columns are zero."""
+import hashlib
+
+import numpy as np
+import pytest
+import torch
+
+from tests import fixtures as fx
+
+pytestmark = pytest.mark.gpu
+P64, P128 = fx.P64, fx.P128
+RINV = pow(2**64, -1, P64)
+
+
+def _horner(coeffs, x, p):
+    acc = 0
+    for c in reversed(coeffs):
+        acc = (acc * x + c) % p
+    return acc
+
+
+def _committer(field, hash_id, n, blowup, cols_per_trace):
+    from starkpack_winterfell_b200.device import TraceCommitter
+
+    return TraceCommitter(field, hash_id, n, blowup, cols_per_trace, device="cuda:0")
+
+
+def _merkle_path_ok(h, nodes, leaves, k, root):
+    """crypto/src/merkle/mod.rs:194-220 style: climb from leaf k to the root with the sibling at each level."""
+    H = (lambda b: __import__("blake3").blake3(b).digest()) if h == 0 else (lambda b: hashlib.sha3_256(b).digest())
+    L = leaves.shape[0]
+    sib = bytes(leaves[k ^ 1])
+    cur = bytes(leaves[k])
+    v = H(cur + sib) if k % 2 == 0 else H(sib + cur)
+    idx = (L + k) >> 1
+    while idx > 1:
+        assert v == bytes(nodes[idx])
+        s = bytes(nodes[idx ^ 1])
+        v = H(v + s) if idx % 2 == 0 else H(s + v)
+        idx >>= 1
+    return v == root
+
+
+def test_config2_full_size_properties():
+    import bench
+
+    n, C_, B = 1 << 22, 100, 8
+    tc = _committer(0, 0, n, B, [C_])
+    tc.cols.copy_(bench.synth_trace_device(torch, C_, n, bench.SEED, tc.device))
+    tc.commit()
+    torch.cuda.synchronize()
+    root = tc.root()
+    tc.commit()  # idempotent
+    torch.cuda.synchronize()
+    assert tc.root() == root
+    L = n * B
+    g_lde = pow(7277203076849721926, 1 << (32 - 25), P64)
+    g_tr = pow(g_lde, B, P64)
+    rng = np.random.default_rng(3)
+    lde = tc.ldes[0]
+    assert int(lde[:, C_:, :].abs().max().item()) == 0  # pad columns 100..103 are zero (row_matrix.rs:110-133)
+    for c in (0, 57, 99):
+        coeffs = [int(x) * RINV % P64 for x in tc.polys[c, :, 0].cpu().numpy().view(np.uint64)]
+        for r in (0, 1, int(rng.integers(0, n))):  # polys evaluate back to the trace (trace/tests.rs:63-80)
+            want = int(tc.cols[c, r, 0].cpu().numpy().view(np.uint64)) * RINV % P64
+            assert _horner(coeffs, pow(g_tr, r, P64), P64) == want
+        for k in (0, 5, L - 1, int(rng.integers(0, L))):  # LDE == P(offset * g^k) (matrix/tests.rs:27-39)
+            got = int(lde[k, c, 0].cpu().numpy().view(np.uint64)) * RINV % P64
+            assert _horner(coeffs, 7 * pow(g_lde, k, P64) % P64, P64) == got
+    import blake3
+
+    leaves = tc.leaves.cpu().numpy()
+    nodes = tc.nodes.cpu().numpy()
+    for k in (0, 1, L - 1, *[int(x) for x in rng.integers(0, L, 5)]):
+        row = lde[k, :C_, 0].cpu().numpy().view(np.uint64)
+        data = b"".join((int(x) * RINV % P64).to_bytes(8, "little") for x in row)  # as_int().to_le_bytes(), F4
+        assert blake3.blake3(data).digest() == bytes(leaves[k])
+        assert _merkle_path_ok(0, nodes, leaves, k, root)
+    assert not nodes[0].any() and bytes(nodes[1]) == root
+
+
+@pytest.mark.parametrize("name,hash_id,traces", [
+    ("config1_fib", 0, 1), ("config3_rescue_shape", 1, 1), ("config4_starkpack8", 0, 8)])
+def test_f128_configs_full_size_vs_oracle(oracle, name, hash_id, traces):
+    n, B = 1 << 20, 8
+    if name == "config3_rescue_shape":
+        trs = [fx.synth_f128(0xC0FFEE03, 4, n)]  # uniform stand-in for the rescue chain states
+    else:
+        # fib recurrence of prover/src/tests/mod.rs:17-29 from start values (t+1, t+1); vectorised by 2x2 matrix powers is
+        # overkill here: generate with the scalar recurrence once per trace at 2^14 rows and tile with distinct seeds
+        trs = []
+        for t in range(traces):
+            base = fx.fib_trace_f128(1 << 12, (t + 1, t + 1))
+            rest = fx.synth_f128(100 + t, 2, n - (1 << 12))
+            trs.append(np.concatenate([base, rest], axis=1))
+    cols = [t.shape[0] for t in trs]
+    tc = _committer(1, hash_id, n, B, cols)
+    allc = np.concatenate(trs, axis=0)
+    tc.cols.copy_(torch.from_numpy(np.ascontiguousarray(allc).view(np.int64)).to(tc.device))
+    tc.commit()
+    torch.cuda.synchronize()
+    want = oracle.commit_trace(1, hash_id, trs, B, want=("lde", "nodes"))
+    assert tc.root() == bytes(want["root"])
+    assert np.array_equal(tc.nodes.cpu().numpy(), want["nodes"])
+    for t in range(len(trs)):
+        assert np.array_equal(tc.ldes[t].cpu().numpy().view(np.uint64), want["lde"][t])
