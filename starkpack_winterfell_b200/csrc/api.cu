@@ -482,6 +482,7 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
   a.n_traces = n_traces;
   a.rows = rows;
   a.leaves = d_leaves;
+  a.one = 1;
   uint64_t off = 0;
   for (uint32_t t = 0; t < n_traces; t++) {
     if (elems[t] > row_widths[t] || elems[t] == 0) return fail(WG_ERR_ARG, "elems_per_row must be in 1..row_width");
@@ -494,10 +495,14 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
   a.unit_off[n_traces] = (uint32_t)off;
   const unsigned blocks = cdiv(rows, 32 * HASH_WARPS);
   ProfScope ps(PH_HASH, stream);
-  if (hash == WG_HASH_BLAKE3_256)
-    hash_rows_kernel<F, HASH_BLAKE3_256><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
-  else
-    hash_rows_kernel<F, HASH_SHA3_256><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+  if (hash == WG_HASH_BLAKE3_256) {
+    if (off * 8 <= 1024)
+      hash_rows_kernel<F, HASH_BLAKE3_256, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+    else
+      hash_rows_kernel<F, HASH_BLAKE3_256, true><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+  } else {
+    hash_rows_kernel<F, HASH_SHA3_256, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+  }
   CUDA_TRY(cudaGetLastError());
   g_launches++;
   return WG_OK;
@@ -508,16 +513,16 @@ static int merkle_dev_t(const uint8_t* d_leaves, uint64_t n_leaves, uint8_t* d_n
   uint4* nodes = reinterpret_cast<uint4*>(d_nodes);
   uint64_t n = n_leaves / 2;
   ProfScope ps(PH_MERKLE, stream);
-  merkle_level_kernel<HASH><<<cdiv(n, 256), 256, 0, stream>>>(reinterpret_cast<const uint4*>(d_leaves), nodes + 2 * n, n);
+  merkle_level_kernel<HASH><<<cdiv(n, 256), 256, 0, stream>>>(reinterpret_cast<const uint4*>(d_leaves), nodes + 2 * n, n, 1u);
   CUDA_TRY(cudaGetLastError());
   g_launches++;
   while (n > 1024) {
-    merkle_level_kernel<HASH><<<cdiv(n / 2, 256), 256, 0, stream>>>(nodes + 2 * n, nodes + n, n / 2);
+    merkle_level_kernel<HASH><<<cdiv(n / 2, 256), 256, 0, stream>>>(nodes + 2 * n, nodes + n, n / 2, 1u);
     CUDA_TRY(cudaGetLastError());
     g_launches++;
     n /= 2;
   }
-  merkle_top_kernel<HASH><<<1, 512, 0, stream>>>(nodes, (uint32_t)n);
+  merkle_top_kernel<HASH><<<1, 512, 0, stream>>>(nodes, (uint32_t)n, 1u);
   CUDA_TRY(cudaGetLastError());
   g_launches++;
   return WG_OK;

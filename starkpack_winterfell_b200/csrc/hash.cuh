@@ -24,16 +24,31 @@ WG_HD uint32_t rotr32(uint32_t x, int n) {
 #endif
 }
 
-#define WG_B3_G(a, b, c, d, mx, my) \
-  do {                              \
-    a = a + b + (mx);               \
-    d = rotr32(d ^ a, 16);          \
-    c = c + d;                      \
-    b = rotr32(b ^ c, 12);          \
-    a = a + b + (my);               \
-    d = rotr32(d ^ a, 8);           \
-    c = c + d;                      \
-    b = rotr32(b ^ c, 7);           \
+// 32-bit add routed to the FMA pipe on the device: `one` is an opaque run-time 1 (a kernel argument), so ptxas keeps
+// a*one+b as IMAD instead of folding it back into IADD3. BLAKE3's G is 12 ALU-pipe instructions per call when written
+// with plain adds (the ALU pipe is the measured bottleneck of the hash kernels, FMA pipe ~15 % busy); with the six
+// adds as IMADs it is 8 ALU + 6 FMA.
+WG_HD uint32_t b3_add(uint32_t a, uint32_t b, uint32_t one) {
+#if defined(__CUDA_ARCH__)
+  uint32_t r;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(one), "r"(b));
+  return r;
+#else
+  (void)one;
+  return a + b;
+#endif
+}
+
+#define WG_B3_G(a, b, c, d, mx, my)               \
+  do {                                            \
+    a = b3_add(b3_add(a, b, one), (mx), one);     \
+    d = rotr32(d ^ a, 16);                        \
+    c = b3_add(c, d, one);                        \
+    b = rotr32(b ^ c, 12);                        \
+    a = b3_add(b3_add(a, b, one), (my), one);     \
+    d = rotr32(d ^ a, 8);                         \
+    c = b3_add(c, d, one);                        \
+    b = rotr32(b ^ c, 7);                         \
   } while (0)
 
 #define WG_B3_ROUND(m0, m1, m2, m3, m4, m5, m6, m7, m8, m9, m10, m11, m12, m13, m14, m15) \
@@ -51,7 +66,8 @@ WG_HD uint32_t rotr32(uint32_t x, int n) {
 // cv <- first 8 words of compress(cv, m, counter, block_len, flags). The seven message schedules are the
 // BLAKE3 permutation [2,6,3,10,7,0,4,13,1,11,12,5,9,14,15,8] applied repeatedly, written out so that the
 // message words stay in fixed registers.
-WG_HD void b3_compress(uint32_t cv[8], const uint32_t m[16], uint64_t counter, uint32_t block_len, uint32_t flags) {
+WG_HD void b3_compress(uint32_t cv[8], const uint32_t m[16], uint64_t counter, uint32_t block_len, uint32_t flags,
+                        uint32_t one = 1) {
   uint32_t v0 = cv[0], v1 = cv[1], v2 = cv[2], v3 = cv[3], v4 = cv[4], v5 = cv[5], v6 = cv[6], v7 = cv[7];
   uint32_t v8 = 0x6A09E667u, v9 = 0xBB67AE85u, v10 = 0x3C6EF372u, v11 = 0xA54FF53Au;
   uint32_t v12 = (uint32_t)counter, v13 = (uint32_t)(counter >> 32), v14 = block_len, v15 = flags;
@@ -84,7 +100,7 @@ WG_HD void b3_iv(uint32_t cv[8]) {
 }
 
 // parent node: compress(IV, left || right, 0, 64, PARENT | extra)
-WG_HD void b3_parent(const uint32_t left[8], uint32_t right_inout[8], uint32_t extra_flags) {
+WG_HD void b3_parent(const uint32_t left[8], uint32_t right_inout[8], uint32_t extra_flags, uint32_t one = 1) {
   uint32_t m[16];
 #pragma unroll
   for (int i = 0; i < 8; i++) {
@@ -92,24 +108,26 @@ WG_HD void b3_parent(const uint32_t left[8], uint32_t right_inout[8], uint32_t e
     m[8 + i] = right_inout[i];
   }
   b3_iv(right_inout);
-  b3_compress(right_inout, m, 0, 64, B3_PARENT | extra_flags);
+  b3_compress(right_inout, m, 0, 64, B3_PARENT | extra_flags, one);
 }
 
 // Hash merge: hash(left32 || right32), a single 64-byte block (Hasher::merge, blake/mod.rs:31-33).
-WG_HD void b3_merge(const uint32_t in16[16], uint32_t out[8]) {
+WG_HD void b3_merge(const uint32_t in16[16], uint32_t out[8], uint32_t one = 1) {
   b3_iv(out);
-  b3_compress(out, in16, 0, 64, B3_CHUNK_START | B3_CHUNK_END | B3_ROOT);
+  b3_compress(out, in16, 0, 64, B3_CHUNK_START | B3_CHUNK_END | B3_ROOT, one);
 }
 
 // Streaming BLAKE3 over an input of known length: feed() takes consecutive 64-byte blocks (zero padded).
 // Single-chunk inputs (<= 1024 B: every config except 2^24 x 256) never touch the cv stack.
 constexpr int B3_MAX_STACK = 12;  // rows up to 4 MiB
-struct B3Stream {
+template <bool MULTI>
+struct B3StreamT {
   uint32_t cv[8];
-  uint32_t stack[B3_MAX_STACK][8];
+  uint32_t stack[MULTI ? B3_MAX_STACK : 1][8];  // single-chunk inputs never touch it
   int sp;
-  uint32_t nbytes, pos, nchunks;
-  WG_HD void init(uint32_t nbytes_) {
+  uint32_t nbytes, pos, nchunks, one;
+  WG_HD void init(uint32_t nbytes_, uint32_t one_ = 1) {
+    one = one_;
     nbytes = nbytes_;
     pos = 0;
     sp = 0;
@@ -124,14 +142,14 @@ struct B3Stream {
     uint32_t flags = (off == 0 ? B3_CHUNK_START : 0) | (last_in_chunk ? B3_CHUNK_END : 0);
     if (nchunks == 1 && last_in_chunk) flags |= B3_ROOT;
     if (off == 0) b3_iv(cv);
-    b3_compress(cv, m, c, blen, flags);
+    b3_compress(cv, m, c, blen, flags, one);
     pos += 64;
-    if (last_in_chunk && nchunks > 1) {
+    if (MULTI && last_in_chunk && nchunks > 1) {
       if (c + 1 < nchunks) {
         uint32_t total = c + 1;
         while ((total & 1) == 0) {
           sp--;
-          b3_parent(stack[sp], cv, 0);
+          b3_parent(stack[sp], cv, 0, one);
           total >>= 1;
         }
         for (int i = 0; i < 8; i++) stack[sp][i] = cv[i];
@@ -140,7 +158,7 @@ struct B3Stream {
       } else {
         while (sp > 0) {
           sp--;
-          b3_parent(stack[sp], cv, sp == 0 ? B3_ROOT : 0);
+          b3_parent(stack[sp], cv, sp == 0 ? B3_ROOT : 0, one);
         }
         pos = nbytes;
       }
@@ -148,10 +166,12 @@ struct B3Stream {
   }
 };
 
+typedef B3StreamT<true> B3Stream;
+
 // Digest of `nbytes` (multiple of 4) delivered by ld(word_index) -> uint32 (little-endian words).
 template <class LD>
 WG_HD void b3_hash_words(LD ld, uint32_t nbytes, uint32_t out[8]) {
-  B3Stream st;
+  B3StreamT<true> st;
   st.init(nbytes);
   const uint32_t nwords = nbytes / 4;
   uint32_t w0 = 0;

@@ -28,11 +28,13 @@ struct RowHashArgs {
   uint32_t n_traces;
   uint64_t rows;
   uint8_t* leaves;  // rows x 32 bytes
+  uint32_t one;     // run-time 1 (see b3_add)
 };
 
 constexpr int HASH_WARPS = 8;
 
-template <class F, int HASH>
+// MULTI = rows longer than one 1024-byte BLAKE3 chunk (needs the chaining-value stack)
+template <class F, int HASH, bool MULTI>
 __global__ void __launch_bounds__(HASH_WARPS * 32) hash_rows_kernel(const RowHashArgs A) {
   constexpr int SU = HASH == HASH_BLAKE3_256 ? 16 : 17;  // 8-byte units per slab
   constexpr int PITCH = 2 * SU + 1;                      // words; odd => conflict-free row reads
@@ -44,10 +46,10 @@ __global__ void __launch_bounds__(HASH_WARPS * 32) hash_rows_kernel(const RowHas
   const uint32_t units_total = A.unit_off[A.n_traces];
   const uint32_t nbytes = units_total * 8;
 
-  B3Stream b3;
+  B3StreamT<MULTI> b3;
   uint64_t ks[25];
   if (HASH == HASH_BLAKE3_256) {
-    b3.init(nbytes);
+    b3.init(nbytes, A.one);
   } else {
 #pragma unroll
     for (int i = 0; i < 25; i++) ks[i] = 0;
@@ -55,24 +57,31 @@ __global__ void __launch_bounds__(HASH_WARPS * 32) hash_rows_kernel(const RowHas
   bool sha_done = false;
 
   for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done); u0 += SU) {
-    // ---- stage SU units of each of the warp's 32 rows
-    for (int idx = lane; idx < 32 * SU; idx += 32) {
+    // ---- stage SU units of each of the warp's 32 rows: issue all SU loads first (one long-scoreboard wait per
+    // slab instead of one per element), then convert and store
+    uint64_t vals[SU];
+#pragma unroll
+    for (int it = 0; it < SU; it++) {
+      const int idx = lane + 32 * it;
       const int r = idx / SU, u = idx - r * SU;
       const uint32_t gu = u0 + u;
       const uint64_t row = row0 + r;
       uint64_t v = 0;
       if (gu < units_total && row < A.rows) {
         uint32_t t = 0;
-        while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
+        if (A.n_traces > 1)
+          while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
         const uint32_t lu = gu - A.unit_off[t];
-        if (F::kFieldId == 0) {
-          const uint64_t* p = (const uint64_t*)A.lde[t];
-          v = Gl64::as_int(p[row * A.row_width[t] + lu]);
-        } else {
-          const uint64_t* p = (const uint64_t*)A.lde[t];
-          v = p[row * A.row_width[t] * 2 + lu];
-        }
+        const uint64_t* p = (const uint64_t*)A.lde[t];
+        v = __ldg(p + row * A.row_width[t] * (F::kElemBytes / 8) + lu);
       }
+      vals[it] = v;
+    }
+#pragma unroll
+    for (int it = 0; it < SU; it++) {
+      const int idx = lane + 32 * it;
+      const int r = idx / SU, u = idx - r * SU;
+      const uint64_t v = F::kFieldId == 0 ? Gl64::as_int(vals[it]) : vals[it];
       slab[r * PITCH + 2 * u] = (uint32_t)v;
       slab[r * PITCH + 2 * u + 1] = (uint32_t)(v >> 32);
     }
@@ -120,9 +129,9 @@ __global__ void __launch_bounds__(HASH_WARPS * 32) hash_rows_kernel(const RowHas
 
 // ---------------------------------------------------------------------------------------------- Merkle
 template <int HASH>
-__device__ __forceinline__ void merge64(const uint32_t in16[16], uint32_t out[8]) {
+__device__ __forceinline__ void merge64(const uint32_t in16[16], uint32_t out[8], uint32_t one) {
   if (HASH == HASH_BLAKE3_256) {
-    b3_merge(in16, out);
+    b3_merge(in16, out, one);
   } else {
     sha3_256_lanes([&](uint32_t i) { return (uint64_t)in16[2 * i] | ((uint64_t)in16[2 * i + 1] << 32); }, 64, out);
   }
@@ -131,7 +140,7 @@ __device__ __forceinline__ void merge64(const uint32_t in16[16], uint32_t out[8]
 // parents[i] = H(children[2i] || children[2i+1]), i < n_parents
 template <int HASH>
 __global__ void __launch_bounds__(256) merkle_level_kernel(const uint4* __restrict__ children, uint4* __restrict__ parents,
-                                                           uint64_t n_parents) {
+                                                           uint64_t n_parents, uint32_t one) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_parents) return;
   uint32_t m[16], o[8];
@@ -143,7 +152,7 @@ __global__ void __launch_bounds__(256) merkle_level_kernel(const uint4* __restri
     m[4 * k + 2] = v.z;
     m[4 * k + 3] = v.w;
   }
-  merge64<HASH>(m, o);
+  merge64<HASH>(m, o, one);
   parents[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
   parents[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
 }
@@ -151,7 +160,7 @@ __global__ void __launch_bounds__(256) merkle_level_kernel(const uint4* __restri
 // Finishes the tree in one block: nodes[n .. 2n) hold level n (n <= 1024 a power of two); computes
 // nodes[n/2 .. n), ..., nodes[1], and zeroes nodes[0].
 template <int HASH>
-__global__ void __launch_bounds__(512) merkle_top_kernel(uint4* nodes, uint32_t n) {
+__global__ void __launch_bounds__(512) merkle_top_kernel(uint4* nodes, uint32_t n, uint32_t one) {
   for (uint32_t lvl = n / 2; lvl >= 1; lvl >>= 1) {
     for (uint32_t i = threadIdx.x; i < lvl; i += blockDim.x) {
       const uint32_t node = lvl + i;
@@ -164,7 +173,7 @@ __global__ void __launch_bounds__(512) merkle_top_kernel(uint4* nodes, uint32_t 
         m[4 * k + 2] = v.z;
         m[4 * k + 3] = v.w;
       }
-      merge64<HASH>(m, o);
+      merge64<HASH>(m, o, one);
       nodes[2 * node] = make_uint4(o[0], o[1], o[2], o[3]);
       nodes[2 * node + 1] = make_uint4(o[4], o[5], o[6], o[7]);
     }
