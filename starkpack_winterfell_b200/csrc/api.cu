@@ -747,6 +747,33 @@ static int h_hash_rows(int hash, const void* rows_host, uint64_t rows, uint64_t 
   return WG_OK;
 }
 
+// Device arena + two streams kept across host-pointer commits: a 2^22 x 100 commit needs 64 GB of device buffers
+// and cudaMalloc/cudaFree of that per call costs tens of milliseconds. Calls are serialised by g_commit_mu.
+static std::mutex g_commit_mu;
+static char* g_arena = nullptr;
+static size_t g_arena_bytes = 0;
+static cudaStream_t g_s_compute = nullptr, g_s_copy = nullptr;
+static cudaEvent_t g_ev[3] = {nullptr, nullptr, nullptr};
+
+static int arena_reserve(size_t bytes) {
+  if (!g_s_compute) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&g_s_compute, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&g_s_copy, cudaStreamNonBlocking));
+    for (auto& e : g_ev) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  if (bytes <= g_arena_bytes) return WG_OK;
+  if (g_arena) cudaFree(g_arena);
+  g_arena = nullptr;
+  g_arena_bytes = 0;
+  cudaError_t e = cudaMalloc(&g_arena, bytes);
+  if (e != cudaSuccess) return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+  g_arena_bytes = bytes;
+  return WG_OK;
+}
+
+// Prover::build_trace_commitment through host buffers. Copies ride a second stream so that the D2H of the
+// polynomials overlaps the LDE kernels, the D2H of each trace's LDE overlaps the next trace's LDE / the row hashing,
+// and only the tree comes back after the last kernel.
 template <class F>
 static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_traces, const uint32_t* cols_per_trace,
                           const void* const* column_ptrs, void* const* polys_out, void* const* lde_out, uint8_t* leaves_out,
@@ -762,38 +789,66 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   }
   const uint64_t L = n * blowup;
   const size_t colb = n * sizeof(T);
-  DevBuf cols, polys, leaves, nodes, scr;
-  std::vector<DevBuf> ldes(n_traces);
-  WG_TRY(cols.alloc(colb * total_cols));
-  WG_TRY(polys.alloc(colb * total_cols));
-  WG_TRY(leaves.alloc(L * 32));
-  WG_TRY(nodes.alloc(L * 32));
-  uint64_t se = interpolate_scratch_elems<F>((uint32_t)total_cols, n);
+  uint64_t se = interpolate_scratch_elems<F>((uint32_t)(total_cols < 65535 ? total_cols : 65535), n);
   const uint64_t se2 = lde_scratch_elems<F>((uint32_t)max_cols, n, blowup);
   if (se2 > se) se = se2;
-  WG_TRY(scr.alloc(se * sizeof(T)));
-  std::vector<void*> lde_ptrs(n_traces);
+  auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+  size_t need = 2 * al(colb * total_cols) + 2 * al(L * 32) + al(se * sizeof(T) + 16);
+  for (uint32_t t = 0; t < n_traces; t++) need += al(L * ((uint64_t)(cols_per_trace[t] + 7) / 8 * 8) * sizeof(T));
+  std::lock_guard<std::mutex> lk(g_commit_mu);
+  WG_TRY(arena_reserve(need));
+  char* cur = g_arena;
+  auto take = [&](size_t b) {
+    char* r = cur;
+    cur += al(b);
+    return r;
+  };
+  T* cols = (T*)take(colb * total_cols);
+  T* polys = (T*)take(colb * total_cols);
+  uint8_t* leaves = (uint8_t*)take(L * 32);
+  uint8_t* nodes = (uint8_t*)take(L * 32);
+  T* scr = (T*)take(se * sizeof(T) + 16);
+  std::vector<T*> ldes(n_traces);
+  std::vector<uint64_t> rws(n_traces), els(n_traces);
   for (uint32_t t = 0; t < n_traces; t++) {
-    const uint64_t rw = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
-    WG_TRY(ldes[t].alloc(L * rw * sizeof(T)));
-    lde_ptrs[t] = ldes[t].p;
+    rws[t] = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
+    els[t] = cols_per_trace[t];
+    ldes[t] = (T*)take(L * rws[t] * sizeof(T));
   }
+  cudaStream_t sc = g_s_compute, sx = g_s_copy;
   for (uint64_t c = 0; c < total_cols; c++)
-    CUDA_TRY(cudaMemcpyAsync(cols.as<char>() + c * colb, column_ptrs[c], colb, cudaMemcpyHostToDevice, 0));
-  WG_TRY(commit_trace_dev<F>(hash, n, blowup, n_traces, cols_per_trace, cols.as<T>(), polys.as<T>(), lde_ptrs.data(),
-                             leaves.as<uint8_t>(), nodes.as<uint8_t>(), scr.as<T>(), se, 0));
-  if (polys_out)
+    CUDA_TRY(cudaMemcpyAsync((char*)cols + c * colb, column_ptrs[c], colb, cudaMemcpyHostToDevice, sc));
+  for (uint64_t c0 = 0; c0 < total_cols; c0 += 65535) {
+    uint32_t nc = (uint32_t)((total_cols - c0) < 65535 ? (total_cols - c0) : 65535);
+    WG_TRY(interpolate_columns_dev<F>(cols + c0 * n, nc, n, polys + c0 * n, scr, se, sc));
+  }
+  if (polys_out) {
+    CUDA_TRY(cudaEventRecord(g_ev[0], sc));
+    CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[0], 0));
     for (uint64_t c = 0; c < total_cols; c++)
-      CUDA_TRY(cudaMemcpyAsync(polys_out[c], polys.as<char>() + c * colb, colb, cudaMemcpyDeviceToHost, 0));
-  if (lde_out)
-    for (uint32_t t = 0; t < n_traces; t++) {
-      const uint64_t rw = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
-      if (lde_out[t]) CUDA_TRY(cudaMemcpyAsync(lde_out[t], ldes[t].p, L * rw * sizeof(T), cudaMemcpyDeviceToHost, 0));
+      CUDA_TRY(cudaMemcpyAsync(polys_out[c], (char*)polys + c * colb, colb, cudaMemcpyDeviceToHost, sx));
+  }
+  uint64_t c0 = 0;
+  std::vector<const void*> lde_c(n_traces);
+  for (uint32_t t = 0; t < n_traces; t++) {
+    WG_TRY(lde_dev<F>(polys + c0 * n, cols_per_trace[t], n, blowup, generator<F>(), ldes[t], rws[t], scr, se, sc));
+    lde_c[t] = ldes[t];
+    c0 += cols_per_trace[t];
+    if (lde_out && lde_out[t]) {
+      CUDA_TRY(cudaEventRecord(g_ev[1], sc));
+      CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[1], 0));
+      CUDA_TRY(cudaMemcpyAsync(lde_out[t], ldes[t], L * rws[t] * sizeof(T), cudaMemcpyDeviceToHost, sx));
     }
-  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves.p, L * 32, cudaMemcpyDeviceToHost, 0));
-  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes.p, L * 32, cudaMemcpyDeviceToHost, 0));
-  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes.as<uint8_t>() + 32, 32, cudaMemcpyDeviceToHost, 0));
-  CUDA_TRY(cudaStreamSynchronize(0));
+  }
+  WG_TRY(hash_rows_dev<F>(hash, n_traces, lde_c.data(), rws.data(), els.data(), L, leaves, sc));
+  WG_TRY(merkle_dev(hash, leaves, L, nodes, sc));
+  CUDA_TRY(cudaEventRecord(g_ev[2], sc));
+  CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[2], 0));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes + 32, 32, cudaMemcpyDeviceToHost, sx));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves, L * 32, cudaMemcpyDeviceToHost, sx));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes, L * 32, cudaMemcpyDeviceToHost, sx));
+  CUDA_TRY(cudaStreamSynchronize(sx));
+  CUDA_TRY(cudaStreamSynchronize(sc));
   return WG_OK;
 }
 
