@@ -752,14 +752,18 @@ static int h_hash_rows(int hash, const void* rows_host, uint64_t rows, uint64_t 
 static std::mutex g_commit_mu;
 static char* g_arena = nullptr;
 static size_t g_arena_bytes = 0;
-static cudaStream_t g_s_compute = nullptr, g_s_copy = nullptr;
+constexpr int H2D_CHUNKS = 8;
+static cudaStream_t g_s_compute = nullptr, g_s_copy = nullptr, g_s_h2d = nullptr;
 static cudaEvent_t g_ev[3] = {nullptr, nullptr, nullptr};
+static cudaEvent_t g_ev_h2d[H2D_CHUNKS];
 
 static int arena_reserve(size_t bytes) {
   if (!g_s_compute) {
     CUDA_TRY(cudaStreamCreateWithFlags(&g_s_compute, cudaStreamNonBlocking));
     CUDA_TRY(cudaStreamCreateWithFlags(&g_s_copy, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&g_s_h2d, cudaStreamNonBlocking));
     for (auto& e : g_ev) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : g_ev_h2d) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   }
   if (bytes <= g_arena_bytes) return WG_OK;
   if (g_arena) cudaFree(g_arena);
@@ -815,11 +819,15 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
     els[t] = cols_per_trace[t];
     ldes[t] = (T*)take(L * rws[t] * sizeof(T));
   }
-  cudaStream_t sc = g_s_compute, sx = g_s_copy;
-  for (uint64_t c = 0; c < total_cols; c++)
-    CUDA_TRY(cudaMemcpyAsync((char*)cols + c * colb, column_ptrs[c], colb, cudaMemcpyHostToDevice, sc));
-  for (uint64_t c0 = 0; c0 < total_cols; c0 += 65535) {
-    uint32_t nc = (uint32_t)((total_cols - c0) < 65535 ? (total_cols - c0) : 65535);
+  cudaStream_t sc = g_s_compute, sx = g_s_copy, sh = g_s_h2d;
+  // upload in up to H2D_CHUNKS column groups; group i is interpolated while group i+1 is still on the wire
+  const uint64_t per = (total_cols + H2D_CHUNKS - 1) / H2D_CHUNKS;
+  for (uint64_t c0 = 0, k = 0; c0 < total_cols; c0 += per, k++) {
+    const uint32_t nc = (uint32_t)((total_cols - c0) < per ? (total_cols - c0) : per);
+    for (uint64_t c = c0; c < c0 + nc; c++)
+      CUDA_TRY(cudaMemcpyAsync((char*)cols + c * colb, column_ptrs[c], colb, cudaMemcpyHostToDevice, sh));
+    CUDA_TRY(cudaEventRecord(g_ev_h2d[k], sh));
+    CUDA_TRY(cudaStreamWaitEvent(sc, g_ev_h2d[k], 0));
     WG_TRY(interpolate_columns_dev<F>(cols + c0 * n, nc, n, polys + c0 * n, scr, se, sc));
   }
   if (polys_out) {
@@ -849,6 +857,7 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes, L * 32, cudaMemcpyDeviceToHost, sx));
   CUDA_TRY(cudaStreamSynchronize(sx));
   CUDA_TRY(cudaStreamSynchronize(sc));
+  CUDA_TRY(cudaStreamSynchronize(sh));
   return WG_OK;
 }
 
