@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -205,6 +206,11 @@ static int launch_pass(int layout, bool inv, int log_s, const PassArgs<F>& a, di
   return WG_OK;
 }
 static inline unsigned cdiv(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+// tuning knob read from the environment (unset: default)
+static int env_int(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return s && *s ? atoi(s) : dflt;
+}
 
 // ------------------------------------------------------------------------------------------------ phase timing
 // Optional CUDA-event timing of the phases of a commit, on the launching stream (bench.py's roofline figure).
@@ -408,6 +414,12 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
   }
   typename Tables<F>::Two tm;
   WG_TRY(tb.get_tm(log_n, false, &tm));
+  // With room for a 2^nb-entry table next to the tile (at the kernel's resident-block count), pass B' multiplies by
+  // q^m2, q = t_z * w_n^j1, which carries both the low half of the coset shift and the inter-pass twiddle; pass A' is
+  // then left with the direct table t_z^(N2*m1). Otherwise pass A' applies shift and twiddle through two-level tables.
+  const size_t smem_b = ntt_pass_smem<F>(1, nb) + (sizeof(T) << nb);
+  const bool use_q = pm.lb == nb && env_int("WG_LDE_Q", 1) && smem_b * FieldCfg<F>::MIN_BLOCKS <= SMEM_PER_SM;
+  const unsigned walk_a = (unsigned)env_int("WG_WALK_A", 1), walk_b = (unsigned)env_int("WG_WALK_B", 13);
   for (uint64_t c0 = 0; c0 < row_width; c0 += chunk) {
     const uint32_t nc_out = (uint32_t)((row_width - c0) < chunk ? (row_width - c0) : chunk);  // incl. pad columns
     const uint32_t nc_in = c0 >= n_cols ? 0 : (uint32_t)((n_cols - c0) < chunk ? (n_cols - c0) : chunk);
@@ -427,24 +439,30 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
       a.out_jstride = (long long)N2;
       a.nw_in = a.nw_out = (uint32_t)N2;
       WG_TRY(tb.get_tws(na, false, &a.tws));
-      a.has_pm = 1;
       a.pm_lo = pm.lo;
       a.pm_hi = pm.hi;
       a.pm_zstride_lo = pzl;
       a.pm_zstride_hi = pzh;
-      a.pm_s = (uint32_t)N2;
-      a.pm_w = 1;
-      a.pm_lb = pm.lb;
-      a.pm_mask = (uint32_t)(n - 1);
-      a.has_tm = 1;
-      a.tm_lo = tm.lo;
-      a.tm_hi = tm.hi;
-      a.tm_lb = tm.lb;
-      a.tm_mask = (uint32_t)(n - 1);
-      a.tm_w = 1;
+      if (use_q) {
+        a.has_pm = 2;
+      } else {
+        a.has_pm = 1;
+        a.pm_s = (uint32_t)N2;
+        a.pm_w = 1;
+        a.pm_lb = pm.lb;
+        a.pm_mask = (uint32_t)(n - 1);
+        a.has_tm = 1;
+        a.tm_lo = tm.lo;
+        a.tm_hi = tm.hi;
+        a.tm_lb = tm.lb;
+        a.tm_mask = (uint32_t)(n - 1);
+        a.tm_w = 1;
+      }
       const int tw = 1 << pass_log_tw<F>(na);
+      a.ny = nc_in;
+      const unsigned gy = cdiv(nc_in, walk_a ? walk_a : 1);
       ProfScope ps(PH_LDE_A, stream);
-      WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw), nc_in, B), stream));
+      WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw), gy, B), stream));
     }
     {
       // pass B': for each (z, j1) transform over m2 (contiguous) -> rows (j1 + N1*j2)*B + z, columns c0..
@@ -462,9 +480,21 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
       a.nw_in = nc_in;
       a.nw_out = nc_out;
       WG_TRY(tb.get_tws(nb, false, &a.tws));
+      if (use_q && nc_in > 0) {
+        a.has_q = 1;
+        a.q_z = pm.lo + 1;  // t_z = first power of coset z's table
+        a.q_zstride = pzl;
+        a.q_y = 1;
+        a.tm_lo = tm.lo;
+        a.tm_hi = tm.hi;
+        a.tm_lb = tm.lb;
+        a.tm_mask = (uint32_t)(n - 1);
+      }
       const int tw = 1 << pass_log_tw<F>(nb);
+      a.nx = cdiv(nc_out, tw);
+      const unsigned gx = cdiv(a.nx, walk_b ? walk_b : 1);
       ProfScope ps(PH_LDE_B, stream);
-      WG_TRY(launch_pass<F>(1, false, nb, a, dim3(cdiv(nc_out, tw), (unsigned)N1, B), stream));
+      WG_TRY(launch_pass<F>(1, false, nb, a, dim3(gx, (unsigned)N1, B), stream));
     }
   }
   return WG_OK;

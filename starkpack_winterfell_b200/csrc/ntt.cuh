@@ -49,7 +49,19 @@ struct PassArgs {
   uint32_t tm_w, tm_y, tm_lb, tm_mask;
   // optional constant post-scale (n^-1 when no tm table carries it)
   T post_const;
+  // has_pm: 0 none, 1 two-level table above, 2 direct: x[s] *= pm_hi[z*pm_zstride_hi + s]
   int has_pm, has_tm, has_const;
+  // optional per-block geometric pre-multiplication x[s] *= q^s (LAYOUT 1 only) with
+  // q = q_z[z*q_zstride] * TM^(y*q_y): the table q^0..q^(S-1) is built in shared memory once per (y, z) and shared by
+  // every tile the block walks along x. This is how the LDE folds the coset shift t_z^m2 and the inter-pass twiddle
+  // w_N^(j1*m2) into one multiplication (q = t_z * w_N^j1).
+  int has_q;
+  const T* q_z;
+  long long q_zstride;
+  uint32_t q_y;
+  // a block walks x = blockIdx.x, blockIdx.x + gridDim.x, ... < nx and y likewise < ny (0: one tile per block);
+  // the in-block twiddle table is loaded once per block
+  uint32_t nx, ny;
 };
 
 // ---------------------------------------------------------------------------------------------- radix butterflies
@@ -164,7 +176,8 @@ __device__ __forceinline__ typename F::T table2(const typename F::T* __restrict_
 // ---------------------------------------------------------------------------------------------- one register step
 template <class F, int LOG_S, int LAYOUT, bool INV, int U>
 __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* tile, const typename F::T* tws,
-                                          long long in_base, long long out_base, uint32_t w0) {
+                                          const typename F::T* qtab, long long in_base, long long out_base, uint32_t w0,
+                                          uint32_t y) {
   typedef typename F::T T;
   typedef PassCfg<F, LOG_S, LAYOUT> C;
   constexpr int LR = C::lr(U);
@@ -195,7 +208,7 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
         const T* src = A.in + in_base + (long long)wg * A.in_wstride;
 #pragma unroll
         for (int r = 0; r < R; r++) a[r] = src[(long long)(s0 + (r << LOGP)) * A.in_sstride];
-        if (A.has_pm) {
+        if (A.has_pm == 1) {
           const T* lo = A.pm_lo + (long long)blockIdx.z * A.pm_zstride_lo;
           const T* hi = A.pm_hi + (long long)blockIdx.z * A.pm_zstride_hi;
 #pragma unroll
@@ -203,6 +216,17 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
             uint32_t e = ((uint32_t)(s0 + (r << LOGP)) * A.pm_s + wg * A.pm_w) & A.pm_mask;
             if (e) a[r] = F::mul(a[r], table2<F>(lo, hi, A.pm_lb, e));
           }
+        } else if (A.has_pm == 2) {
+          const T* hi = A.pm_hi + (long long)blockIdx.z * A.pm_zstride_hi;
+          T f[R];
+#pragma unroll
+          for (int r = 0; r < R; r++) f[r] = hi[s0 + (r << LOGP)];
+#pragma unroll
+          for (int r = 0; r < R; r++) a[r] = F::mul(a[r], f[r]);
+        }
+        if (LAYOUT == 1 && A.has_q) {
+#pragma unroll
+          for (int r = 0; r < R; r++) a[r] = F::mul(a[r], qtab[s0 + (r << LOGP)]);
         }
       } else {
 #pragma unroll
@@ -250,7 +274,7 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
         T* dst = A.out + out_base + (long long)wg * A.out_wstride;
         uint32_t ebase = 0, estep = 0;
         if (A.has_tm) {
-          uint32_t f = wg * A.tm_w + blockIdx.y * A.tm_y;
+          uint32_t f = wg * A.tm_w + y * A.tm_y;
           ebase = (uint32_t)nat0 * f;
           estep = f << shift_out;
         }
@@ -277,24 +301,45 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* tile = reinterpret_cast<T*>(smem_raw);
   T* tws = tile + C::TILE_ELEMS;
+  T* qtab = tws + C::TWS_ELEMS;  // S entries, present when has_q
   if (C::NSTEPS > 1) {
     for (int i = threadIdx.x; i < C::TWS_ELEMS; i += C::NT) tws[i] = A.tws[i];
   }
-  const uint32_t w0 = blockIdx.x * C::TW;
-  const long long in_base = (long long)blockIdx.y * A.in_ystride + (long long)blockIdx.z * A.in_zstride;
-  const long long out_base = (long long)blockIdx.y * A.out_ystride + (long long)blockIdx.z * A.out_zstride;
-  pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, in_base, out_base, w0);
-  if (C::NSTEPS > 1) {
-    __syncthreads();
-    pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 1 ? 1 : 0)>(A, tile, tws, in_base, out_base, w0);
-  }
-  if (C::NSTEPS > 2) {
-    __syncthreads();
-    pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 2 ? 2 : 0)>(A, tile, tws, in_base, out_base, w0);
-  }
-  if (C::NSTEPS > 3) {
-    __syncthreads();
-    pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 3 ? 3 : 0)>(A, tile, tws, in_base, out_base, w0);
+  const uint32_t nx = A.nx ? A.nx : gridDim.x, ny = A.ny ? A.ny : gridDim.y;
+  for (uint32_t y = blockIdx.y; y < ny; y += gridDim.y) {
+    if (LAYOUT == 1 && A.has_q) {
+      // qtab[i] = q^i by doubling: level k appends q^(2^k) * qtab[0 .. 2^k)
+      T qp = table2<F>(A.tm_lo, A.tm_hi, A.tm_lb, (y * A.q_y) & A.tm_mask);
+      if (A.q_z) qp = F::mul(qp, A.q_z[(long long)blockIdx.z * A.q_zstride]);
+      __syncthreads();  // previous y's readers are done
+      if (threadIdx.x == 0) qtab[0] = F::one();
+      __syncthreads();
+#pragma unroll 1
+      for (int k = 0; k < LOG_S; k++) {
+        for (int i = threadIdx.x; i < (1 << k); i += C::NT) qtab[(1 << k) + i] = F::mul(qtab[i], qp);
+        qp = F::mul(qp, qp);
+        __syncthreads();
+      }
+    }
+    const long long in_base = (long long)y * A.in_ystride + (long long)blockIdx.z * A.in_zstride;
+    const long long out_base = (long long)y * A.out_ystride + (long long)blockIdx.z * A.out_zstride;
+    for (uint32_t x = blockIdx.x; x < nx; x += gridDim.x) {
+      const uint32_t w0 = x * C::TW;
+      pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, qtab, in_base, out_base, w0, y);
+      if (C::NSTEPS > 1) {
+        __syncthreads();
+        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 1 ? 1 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y);
+      }
+      if (C::NSTEPS > 2) {
+        __syncthreads();
+        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 2 ? 2 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y);
+      }
+      if (C::NSTEPS > 3) {
+        __syncthreads();
+        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 3 ? 3 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y);
+      }
+      if (C::NSTEPS > 1) __syncthreads();  // the tile is rewritten by the next walk step
+    }
   }
 }
 

@@ -12,6 +12,11 @@ constexpr int MIN_LOG_S_STRIDED = 6;  // strided passes are only used for N >= 2
 template <class F>
 cudaError_t launch_ntt_pass(int layout, bool inv, int log_s, const PassArgs<F>& a, dim3 grid, cudaStream_t stream);
 
+// dynamic shared memory of the (layout, log_s) instantiation without the optional q table
+template <class F>
+size_t ntt_pass_smem(int layout, int log_s);
+constexpr size_t SMEM_PER_SM = 227 * 1024;
+
 template <class F>
 inline int pass_log_tw(int log_s) {
   int l = FieldCfg<F>::LOG_TILE - log_s;
@@ -23,14 +28,40 @@ inline int pass_log_tw(int log_s) {
   static cudaError_t launch_one_##F(const PassArgs<F>& a, dim3 grid, cudaStream_t stream) {                     \
     typedef PassCfg<F, LOG_S, LAYOUT> C;                                                                        \
     static bool attr_set = false;                                                                               \
-    if (!attr_set && C::SMEM_BYTES > 48 * 1024) {                                                               \
+    constexpr size_t QB = LAYOUT == 1 ? sizeof(F::T) << LOG_S : 0;                                              \
+    constexpr size_t MAXB = C::SMEM_BYTES + QB > SMEM_PER_SM ? C::SMEM_BYTES : C::SMEM_BYTES + QB;              \
+    if (!attr_set && MAXB > 48 * 1024) {                                                                        \
       cudaError_t e = cudaFuncSetAttribute(ntt_pass_kernel<F, LOG_S, LAYOUT, INV>,                              \
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES);    \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MAXB);             \
       if (e != cudaSuccess) return e;                                                                           \
       attr_set = true;                                                                                          \
     }                                                                                                           \
-    ntt_pass_kernel<F, LOG_S, LAYOUT, INV><<<grid, C::NT, C::SMEM_BYTES, stream>>>(a);                          \
+    const size_t smem = C::SMEM_BYTES + (a.has_q ? QB : 0);                                                     \
+    if (smem > MAXB) return cudaErrorInvalidValue;                                                              \
+    ntt_pass_kernel<F, LOG_S, LAYOUT, INV><<<grid, C::NT, smem, stream>>>(a);                                   \
     return cudaGetLastError();                                                                                  \
+  }                                                                                                             \
+  template <int LAYOUT>                                                                                         \
+  static size_t smem_sz_##F(int log_s) {                                                                        \
+    switch (log_s) {                                                                                            \
+      case 1: return PassCfg<F, 1, LAYOUT>::SMEM_BYTES;                                                         \
+      case 2: return PassCfg<F, 2, LAYOUT>::SMEM_BYTES;                                                         \
+      case 3: return PassCfg<F, 3, LAYOUT>::SMEM_BYTES;                                                         \
+      case 4: return PassCfg<F, 4, LAYOUT>::SMEM_BYTES;                                                         \
+      case 5: return PassCfg<F, 5, LAYOUT>::SMEM_BYTES;                                                         \
+      case 6: return PassCfg<F, 6, LAYOUT>::SMEM_BYTES;                                                         \
+      case 7: return PassCfg<F, 7, LAYOUT>::SMEM_BYTES;                                                         \
+      case 8: return PassCfg<F, 8, LAYOUT>::SMEM_BYTES;                                                         \
+      case 9: return PassCfg<F, 9, LAYOUT>::SMEM_BYTES;                                                         \
+      case 10: return PassCfg<F, 10, LAYOUT>::SMEM_BYTES;                                                       \
+      case 11: return PassCfg<F, 11, LAYOUT>::SMEM_BYTES;                                                       \
+      case 12: return PassCfg<F, 12, LAYOUT>::SMEM_BYTES;                                                       \
+      default: return 0;                                                                                        \
+    }                                                                                                           \
+  }                                                                                                             \
+  template <>                                                                                                   \
+  size_t ntt_pass_smem<F>(int layout, int log_s) {                                                              \
+    return layout == 0 ? smem_sz_##F<0>(log_s) : smem_sz_##F<1>(log_s);                                         \
   }                                                                                                             \
   template <int LAYOUT, bool INV>                                                                               \
   static cudaError_t launch_sz_##F(int log_s, const PassArgs<F>& a, dim3 grid, cudaStream_t stream) {           \
