@@ -38,6 +38,12 @@ WG_HD void mul64wide(uint64_t a, uint64_t b, uint64_t& hi, uint64_t& lo) {
 // Montgomery words too. On the device add/sub/mont_red are written as 32-bit carry chains in PTX: the
 // straightforward C forms compile to 10 / 10 / 33 SASS instructions, these to 8 / 5 / ~17, and the product's
 // four IMAD.WIDE run on the FMA pipe while the carry chains run on the ALU pipe.
+#if defined(__CUDACC__)
+// run-time 1 and -1: opaque to ptxas, so multiply-adds by them stay IMAD (FMA pipe) instead of being folded to IADD3
+static __constant__ uint32_t K_ONE = 1u;
+static __constant__ uint32_t K_MONE = 0xFFFFFFFFu;
+#endif
+
 struct Gl64 {
   typedef uint64_t T;
   static constexpr int kFieldId = 0;
@@ -52,16 +58,25 @@ struct Gl64 {
   static WG_HD T one() { return EPS; }
   static WG_HD bool is_zero(T a) { return a == 0; }
 
+  // Device add/sub/mul below are written so that every carry-CONSUMING step that does not have to produce a carry is a
+  // multiply-add (mad/madc with the run-time constants K_ONE / K_MONE, which ptxas cannot fold): those issue on the
+  // FMA pipe as IMAD / IMAD.X, while carry-producing steps must be IADD3 on the ALU pipe. The NTT kernels are bound
+  // by integer issue with the ALU pipe the busy one, so this balances the two pipes (about 17 ALU : 16 FMA per
+  // butterfly instead of 22 : 7).
   static WG_HD T add(T a, T b) {
 #if defined(__CUDA_ARCH__)
     // a - (p - b), then + p on borrow (the reference's formulation, f64/mod.rs:314-324)
     uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), d0, d1;
-    asm("{\n\t.reg .u32 m, t0, t1;\n\t"
-        "sub.cc.u32 t0, 1, %4;\n\tsubc.u32 t1, 0xFFFFFFFF, %5;\n\t"
-        "sub.cc.u32 %0, %2, t0;\n\tsubc.cc.u32 %1, %3, t1;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+    asm("{\n\t.reg .u32 m, bit, t0, t1, n0, n1;\n\t"
+        "mad.lo.u32 n0, %4, %7, %7;\n\t"    // ~b0
+        "add.cc.u32 n0, n0, 2;\n\t"          // 1 - b0; carry = no borrow
+        "madc.lo.u32 n1, %5, %7, 0xFFFFFFFE;\n\t"  // ~b1 - 1 + carry = 0xFFFFFFFF - b1 - borrow
+        "sub.cc.u32 t0, %2, n0;\n\tsubc.cc.u32 t1, %3, n1;\n\tsubc.u32 m, 0, 0;\n\t"
+        "mul.lo.u32 bit, m, %7;\n\t"         // borrow as 0/1
+        "add.cc.u32 %0, t0, bit;\n\t"        // + p = (+1, +0xFFFFFFFF + carry)
+        "madc.lo.u32 %1, t1, %6, m;\n\t}"
         : "=&r"(d0), "=&r"(d1)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ONE), "r"(K_MONE));
     return ((uint64_t)d1 << 32) | d0;
 #else
     uint64_t s = a + b;
@@ -72,11 +87,13 @@ struct Gl64 {
   static WG_HD T sub(T a, T b) {
 #if defined(__CUDA_ARCH__)
     uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), d0, d1;
-    asm("{\n\t.reg .u32 m;\n\t"
-        "sub.cc.u32 %0, %2, %4;\n\tsubc.cc.u32 %1, %3, %5;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+    asm("{\n\t.reg .u32 m, bit, t0, t1;\n\t"
+        "sub.cc.u32 t0, %2, %4;\n\tsubc.cc.u32 t1, %3, %5;\n\tsubc.u32 m, 0, 0;\n\t"
+        "mul.lo.u32 bit, m, %7;\n\t"
+        "add.cc.u32 %0, t0, bit;\n\t"
+        "madc.lo.u32 %1, t1, %6, m;\n\t}"
         : "=&r"(d0), "=&r"(d1)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ONE), "r"(K_MONE));
     return ((uint64_t)d1 << 32) | d0;
 #else
     uint64_t d = a - b;
@@ -122,10 +139,12 @@ struct Gl64 {
         "add.cc.u32 l1, l1, w0;\n\taddc.cc.u32 h0, h0, w1;\n\taddc.u32 h1, h1, 0;\n\t"
         "add.cc.u32 a1, l1, t0;\n\t"
         "addc.cc.u32 s0, h0, a1;\n\taddc.u32 s1, h1, 0;\n\t"
-        "sub.cc.u32 %0, s0, t0;\n\tsubc.cc.u32 %1, s1, a1;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+        "sub.cc.u32 s0, s0, t0;\n\tsubc.cc.u32 s1, s1, a1;\n\tsubc.u32 m, 0, 0;\n\t"
+        "mul.lo.u32 u0, m, %7;\n\t"
+        "add.cc.u32 %0, s0, u0;\n\t"
+        "madc.lo.u32 %1, s1, %6, m;\n\t}"
         : "=&r"(r0), "=&r"(r1)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1));
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ONE), "r"(K_MONE));
     return ((uint64_t)r1 << 32) | r0;
 #else
     uint64_t hi, lo;
