@@ -9,7 +9,7 @@ data-path collective; "weak" scaling) — the StarkPack "one trace per GPU" part
   value        device-resident: trace already in HBM, results left in HBM, CUDA events around K steps
   e2e          the same work through the C-ABI host entry point wg_commit_trace with pinned host buffers:
                H2D of the trace and D2H of polys + LDE + leaves + nodes inside the timed region
-  roofline     dominant kernel (LDE contiguous pass), algorithmic bytes / its CUDA-event time
+  roofline     dominant kernel (LDE contiguous pass): SURVEY 8(d) algorithmic bytes it moves / its CUDA-event time
   cpu_baseline the CPU oracle (C + OpenMP restatement of the reference, kind "port") on a bounded sample
   --impl reference : that oracle as the reference arm, on the host cores.
 """
@@ -263,14 +263,23 @@ def run_ours(args):
     peak, peak_src = peaks()
     L = n * BLOWUP
     rw = (COLS + 7) // 8 * 8
-    # dominant kernel = LDE contiguous pass (ntt_pass_kernel<Gl64,11,1,false>): its own compulsory traffic is
-    # one read of the B*N*C intermediate and one write of the L x C LDE words (DESIGN.md "kernels")
-    dom = max(phases, key=lambda k: phases[k][0])
-    kbytes = {"lde_contig": 2 * L * COLS * 8, "lde_strided": n * COLS * 8 + L * COLS * 8,
-              "interp_strided": 2 * n * COLS * 8, "interp_contig": 2 * n * COLS * 8,
-              "hash_rows": L * COLS * 8 + L * 32, "merkle": 2 * L * 32}[dom]
+    # Dominant kernel: the LDE contiguous pass (ntt_pass_kernel<Gl64,11,1,false>) and the LDE strided pass take within a
+    # few percent of each other; the contiguous pass is the one that moves SURVEY 8(d)'s algorithmic bytes (it writes the
+    # L x C LDE words, 26.8 of the 35.7 GB), so it is the one quoted. `achieved` counts ONLY those algorithmic bytes;
+    # `kernel_io_*` also counts the kernel's own compulsory read of the B*N*C intermediate; `traffic` is the DRAM bytes
+    # ncu measured for one launch (profiles/r1_traffic.json).
+    dom = "lde_contig"
+    dom_by_time = max(phases, key=lambda k: phases[k][0])
+    kbytes = L * COLS * 8
+    kio = L * COLS * 8 + L * rw * 8
     dom_ms = phases[dom][0] / max(phases[dom][1], 1)
     achieved = kbytes / (dom_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            traffic = json.load(f)["phases"][dom]["dram_bytes"]
+    except Exception:
+        pass
     alg = algorithmic_bytes(n, COLS, BLOWUP)
     cb = cpu_commit_sample(args.cpu_log_rows) if world == 1 else None
     line = {
@@ -284,8 +293,11 @@ def run_ours(args):
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "root": root_hex,
         "phases_ms": {k: round(v[0], 3) for k, v in phases.items()},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": kbytes, "kernel_ms": dom_ms,
-                     "note": "integer-issue bound, see DESIGN.md; HBM fraction reported as the contract asks"},
+                     "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": kbytes, "kernel_ms": dom_ms,
+                     "kernel_share_of_step": dom_ms / ms, "longest_phase": dom_by_time,
+                     "kernel_io_bytes": kio, "kernel_io_gbs": kio / (dom_ms * 1e-3) / 1e9, "kernel_io_frac": kio / (dom_ms * 1e-3) / 1e9 / peak,
+                     "note": "integer-issue bound (ALU and FMA pipes both ~60% busy, DRAM ~25%), see DESIGN.md; HBM fraction "
+                             "reported as the contract asks"},
         "cpu_baseline": cb,
     }
     print(json.dumps(line), flush=True)

@@ -462,7 +462,12 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
       a.ny = nc_in;
       const unsigned gy = cdiv(nc_in, walk_a ? walk_a : 1);
       ProfScope ps(PH_LDE_A, stream);
-      WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw), gy, B), stream));
+      if (env_int("WG_ZFAST", 1)) {
+        a.zfast = B;
+        WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw) * B, gy, 1), stream));
+      } else {
+        WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw), gy, B), stream));
+      }
     }
     {
       // pass B': for each (z, j1) transform over m2 (contiguous) -> rows (j1 + N1*j2)*B + z, columns c0..

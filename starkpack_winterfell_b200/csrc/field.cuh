@@ -112,10 +112,12 @@ struct Gl64 {
     asm("{\n\t.reg .u32 a1, s0, s1, m;\n\t"
         "add.cc.u32 a1, %3, %2;\n\t"
         "addc.cc.u32 s0, %4, a1;\n\taddc.u32 s1, %5, 0;\n\t"
-        "sub.cc.u32 %0, s0, %2;\n\tsubc.cc.u32 %1, s1, a1;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 %0, %0, m;\n\tsubc.u32 %1, %1, 0;\n\t}"
+        "sub.cc.u32 s0, s0, %2;\n\tsubc.cc.u32 s1, s1, a1;\n\tsubc.u32 m, 0, 0;\n\t"
+        "mul.lo.u32 a1, m, %7;\n\t"
+        "add.cc.u32 %0, s0, a1;\n\t"
+        "madc.lo.u32 %1, s1, %6, m;\n\t}"
         : "=&r"(r0), "=&r"(r1)
-        : "r"(l0), "r"(l1), "r"(h0), "r"(h1));
+        : "r"(l0), "r"(l1), "r"(h0), "r"(h1), "r"(K_ONE), "r"(K_MONE));
     return ((uint64_t)r1 << 32) | r0;
 #else
     uint64_t a = xl + (xl << 32);
@@ -130,7 +132,7 @@ struct Gl64 {
   static WG_HD T mul(T a, T b) {
 #if defined(__CUDA_ARCH__)
     // four 32x32->64 products (IMAD.WIDE, FMA pipe), two carry chains to assemble (h1:h0:l1:t0), then the
-    // Montgomery reduction of mont_red() inline; 17 SASS instructions in total
+    // Montgomery reduction of mont_red() inline; 10 ALU-pipe + 8 FMA-pipe SASS instructions
     uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), r0, r1;
     asm("{\n\t.reg .u64 t, u, v, w;\n\t.reg .u32 t0, t1, u0, u1, v0, v1, w0, w1, l1, h0, h1, a1, s0, s1, m;\n\t"
         "mul.wide.u32 t, %2, %4;\n\tmul.wide.u32 v, %2, %5;\n\tmul.wide.u32 w, %3, %4;\n\tmul.wide.u32 u, %3, %5;\n\t"

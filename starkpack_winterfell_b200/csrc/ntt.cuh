@@ -62,6 +62,9 @@ struct PassArgs {
   // a block walks x = blockIdx.x, blockIdx.x + gridDim.x, ... < nx and y likewise < ny (0: one tile per block);
   // the in-block twiddle table is loaded once per block
   uint32_t nx, ny;
+  // zfast = nz > 0: the grid is (gx*nz, gy, 1) and z = blockIdx.x % nz varies fastest, so the nz blocks that read
+  // the same input tile (the cosets of one polynomial slice) are co-resident and all but one hit in L2
+  uint32_t zfast;
 };
 
 // ---------------------------------------------------------------------------------------------- radix butterflies
@@ -177,7 +180,7 @@ __device__ __forceinline__ typename F::T table2(const typename F::T* __restrict_
 template <class F, int LOG_S, int LAYOUT, bool INV, int U>
 __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* tile, const typename F::T* tws,
                                           const typename F::T* qtab, long long in_base, long long out_base, uint32_t w0,
-                                          uint32_t y) {
+                                          uint32_t y, uint32_t z) {
   typedef typename F::T T;
   typedef PassCfg<F, LOG_S, LAYOUT> C;
   constexpr int LR = C::lr(U);
@@ -209,15 +212,15 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
 #pragma unroll
         for (int r = 0; r < R; r++) a[r] = src[(long long)(s0 + (r << LOGP)) * A.in_sstride];
         if (A.has_pm == 1) {
-          const T* lo = A.pm_lo + (long long)blockIdx.z * A.pm_zstride_lo;
-          const T* hi = A.pm_hi + (long long)blockIdx.z * A.pm_zstride_hi;
+          const T* lo = A.pm_lo + (long long)z * A.pm_zstride_lo;
+          const T* hi = A.pm_hi + (long long)z * A.pm_zstride_hi;
 #pragma unroll
           for (int r = 0; r < R; r++) {
             uint32_t e = ((uint32_t)(s0 + (r << LOGP)) * A.pm_s + wg * A.pm_w) & A.pm_mask;
             if (e) a[r] = F::mul(a[r], table2<F>(lo, hi, A.pm_lb, e));
           }
         } else if (A.has_pm == 2) {
-          const T* hi = A.pm_hi + (long long)blockIdx.z * A.pm_zstride_hi;
+          const T* hi = A.pm_hi + (long long)z * A.pm_zstride_hi;
           T f[R];
 #pragma unroll
           for (int r = 0; r < R; r++) f[r] = hi[s0 + (r << LOGP)];
@@ -305,12 +308,18 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
   if (C::NSTEPS > 1) {
     for (int i = threadIdx.x; i < C::TWS_ELEMS; i += C::NT) tws[i] = A.tws[i];
   }
-  const uint32_t nx = A.nx ? A.nx : gridDim.x, ny = A.ny ? A.ny : gridDim.y;
+  uint32_t bx = blockIdx.x, gx = gridDim.x, z = blockIdx.z;
+  if (A.zfast) {
+    z = bx % A.zfast;
+    bx /= A.zfast;
+    gx /= A.zfast;
+  }
+  const uint32_t nx = A.nx ? A.nx : gx, ny = A.ny ? A.ny : gridDim.y;
   for (uint32_t y = blockIdx.y; y < ny; y += gridDim.y) {
     if (LAYOUT == 1 && A.has_q) {
       // qtab[i] = q^i by doubling: level k appends q^(2^k) * qtab[0 .. 2^k)
       T qp = table2<F>(A.tm_lo, A.tm_hi, A.tm_lb, (y * A.q_y) & A.tm_mask);
-      if (A.q_z) qp = F::mul(qp, A.q_z[(long long)blockIdx.z * A.q_zstride]);
+      if (A.q_z) qp = F::mul(qp, A.q_z[(long long)z * A.q_zstride]);
       __syncthreads();  // previous y's readers are done
       if (threadIdx.x == 0) qtab[0] = F::one();
       __syncthreads();
@@ -321,22 +330,22 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
         __syncthreads();
       }
     }
-    const long long in_base = (long long)y * A.in_ystride + (long long)blockIdx.z * A.in_zstride;
-    const long long out_base = (long long)y * A.out_ystride + (long long)blockIdx.z * A.out_zstride;
-    for (uint32_t x = blockIdx.x; x < nx; x += gridDim.x) {
+    const long long in_base = (long long)y * A.in_ystride + (long long)z * A.in_zstride;
+    const long long out_base = (long long)y * A.out_ystride + (long long)z * A.out_zstride;
+    for (uint32_t x = bx; x < nx; x += gx) {
       const uint32_t w0 = x * C::TW;
-      pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, qtab, in_base, out_base, w0, y);
+      pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, qtab, in_base, out_base, w0, y, z);
       if (C::NSTEPS > 1) {
         __syncthreads();
-        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 1 ? 1 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y);
+        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 1 ? 1 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y, z);
       }
       if (C::NSTEPS > 2) {
         __syncthreads();
-        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 2 ? 2 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y);
+        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 2 ? 2 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y, z);
       }
       if (C::NSTEPS > 3) {
         __syncthreads();
-        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 3 ? 3 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y);
+        pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 3 ? 3 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y, z);
       }
       if (C::NSTEPS > 1) __syncthreads();  // the tile is rewritten by the next walk step
     }
