@@ -334,6 +334,14 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
     const long long out_base = (long long)y * A.out_ystride + (long long)z * A.out_zstride;
     for (uint32_t x = bx; x < nx; x += gx) {
       const uint32_t w0 = x * C::TW;
+      if (w0 >= A.nw_in) {
+        // a tile of zero problems (the LDE's padding columns): the transform of zeros is zeros
+        for (int i = threadIdx.x; i < C::S * C::TW; i += C::NT) {
+          const uint32_t wg = w0 + (uint32_t)(i & (C::TW - 1));
+          if (wg < A.nw_out) A.out[out_base + (long long)wg * A.out_wstride + (long long)(i >> C::LOG_TW) * A.out_jstride] = F::zero();
+        }
+        continue;
+      }
       pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, qtab, in_base, out_base, w0, y, z);
       if (C::NSTEPS > 1) {
         __syncthreads();
