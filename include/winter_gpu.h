@@ -69,6 +69,14 @@ int wg_get_twiddles(int field, uint64_t n, int inverse, void* out);
  * inv_twiddles may be NULL; if given only its length contract (n/2) is assumed. */
 int wg_interpolate_poly(int field, void* evals, uint64_t n, const void* inv_twiddles);
 
+/* fft::interpolate_poly_with_offset (math/src/fft/mod.rs:362-400): in place; coefficient i of the inverse transform is
+ * multiplied by offset^-i, so the result interpolates evaluations taken over the coset offset*<w_n>. */
+int wg_interpolate_poly_with_offset(int field, void* evals, uint64_t n, const void* inv_twiddles, const void* offset);
+
+/* fft::evaluate_poly (math/src/fft/mod.rs:85-116) and fft::serial_fft (:416-440; fft_in_place + permute gives the same
+ * natural-order result): in place, p[k] <- P(w_n^k). */
+int wg_evaluate_poly(int field, void* p, uint64_t n, const void* twiddles);
+
 /* fft::evaluate_poly_with_offset (math/src/fft/mod.rs:171-220): out has n*blowup elements,
  * out[k] = P(offset * w_{n*blowup}^k). offset points at one element in internal representation. */
 int wg_evaluate_poly_with_offset(int field, const void* p, uint64_t n, const void* twiddles, const void* offset,

@@ -750,6 +750,39 @@ static int h_interpolate_columns(const void* const* cols, uint32_t n_cols, uint6
   return WG_OK;
 }
 
+// x[i] *= base^i (two-level table of `base`), the coefficient rescale of fft::interpolate_poly_with_offset
+template <class F>
+__global__ void scale_powers_kernel(typename F::T* x, uint64_t n, const typename F::T* lo, const typename F::T* hi, uint32_t lb) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x[i] = F::mul(x[i], table2<F>(lo, hi, lb, (uint32_t)i));
+}
+
+// fft::interpolate_poly_with_offset (math/src/fft/mod.rs:362-400; serial.rs:78-93): inverse transform, then
+// coefficient i times offset^-i
+template <class F>
+static int h_interpolate_poly_with_offset(void* evals, uint64_t n, const void* offset) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, 1));
+  const T off = offset_from_internal<F>(offset);
+  if (F::is_zero(off)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
+  DevBuf in, out, scr;
+  WG_TRY(in.alloc(n * sizeof(T)));
+  WG_TRY(out.alloc(n * sizeof(T)));
+  const uint64_t se = interpolate_scratch_elems<F>(1, n);
+  WG_TRY(scr.alloc(se * sizeof(T)));
+  CUDA_TRY(cudaMemcpyAsync(in.p, evals, n * sizeof(T), cudaMemcpyHostToDevice, 0));
+  WG_TRY(interpolate_columns_dev<F>(in.as<T>(), 1, n, out.as<T>(), scr.as<T>(), se, 0));
+  typename Tables<F>::Two pm;
+  long long zl, zh;
+  WG_TRY(tables<F>().get_pm(ilog2(n), 0, f_inv<F>(off), &pm, &zl, &zh));
+  scale_powers_kernel<F><<<cdiv(n, 256), 256, 0, 0>>>(out.as<T>(), n, pm.lo, pm.hi, (uint32_t)pm.lb);
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  CUDA_TRY(cudaMemcpyAsync(evals, out.p, n * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
 template <class F>
 static int h_evaluate_polys_over(const void* const* polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset,
                                  void* out, uint64_t row_width) {
@@ -974,6 +1007,28 @@ int wg_interpolate_poly(int field, void* evals, uint64_t n, const void* inv_twid
   const void* in[1] = {evals};
   void* out[1] = {evals};
   WG_FIELD_DISPATCH(field, h_interpolate_columns<Gl64>(in, 1, n, out), h_interpolate_columns<F128>(in, 1, n, out));
+}
+
+int wg_interpolate_poly_with_offset(int field, void* evals, uint64_t n, const void* inv_twiddles, const void* offset) {
+  (void)inv_twiddles;
+  if (!evals || !offset) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_interpolate_poly_with_offset<Gl64>(evals, n, offset), h_interpolate_poly_with_offset<F128>(evals, n, offset));
+}
+
+int wg_evaluate_poly(int field, void* p, uint64_t n, const void* twiddles) {
+  (void)twiddles;
+  if (!p) return fail(WG_ERR_ARG, "null input");
+  WG_TRY(ensure_device());
+  const void* in[1] = {p};
+  if (field == WG_FIELD_F64) {
+    const Gl64::T one = Gl64::one();
+    return h_evaluate_polys_over<Gl64>(in, 1, n, 1, &one, p, 1);
+  } else if (field == WG_FIELD_F128) {
+    const F128::T one = F128::one();
+    return h_evaluate_polys_over<F128>(in, 1, n, 1, &one, p, 1);
+  }
+  return fail(WG_ERR_ARG, "unknown field %d", field);
 }
 
 int wg_evaluate_poly_with_offset(int field, const void* p, uint64_t n, const void* twiddles, const void* offset,

@@ -62,6 +62,44 @@ def evaluate_poly_with_offset(field, p, twiddles, domain_offset, blowup_factor):
     return out
 
 
+def _inplace(v, what):
+    if not (isinstance(v, np.ndarray) and v.dtype == np.uint64 and v.flags.c_contiguous):
+        raise ValueError(f"{what} must be a contiguous uint64 numpy array (modified in place)")
+    return v.shape[0]
+
+
+def evaluate_poly(field, p, twiddles=None):
+    """fft::evaluate_poly (math/src/fft/mod.rs:85-116): IN PLACE, p[k] <- P(w_n^k), natural order."""
+    n = _inplace(p, "p")
+    if twiddles is not None and len(twiddles) * 2 != n:
+        raise ValueError(f"invalid number of twiddles: expected {n // 2} but received {len(twiddles)}")
+    check(lib().wg_evaluate_poly(field, _p(p), n, None))
+
+
+def serial_fft(field, values, twiddles=None):
+    """fft::serial_fft (math/src/fft/mod.rs:416-440): fft_in_place followed by permute, i.e. the natural-order transform."""
+    evaluate_poly(field, values, twiddles)
+
+
+def interpolate_poly_with_offset(field, evaluations, inv_twiddles, domain_offset):
+    """fft::interpolate_poly_with_offset (math/src/fft/mod.rs:362-400): IN PLACE; evaluations were taken over the coset
+    domain_offset * <w_n>. domain_offset is one element in internal representation."""
+    n = _inplace(evaluations, "evaluations")
+    if inv_twiddles is not None and len(inv_twiddles) * 2 != n:
+        raise ValueError(f"invalid number of twiddles: expected {n // 2} but received {len(inv_twiddles)}")
+    off = np.ascontiguousarray(domain_offset, dtype=np.uint64).reshape(-1)
+    check(lib().wg_interpolate_poly_with_offset(field, _p(evaluations), n, None, _p(off)))
+
+
+def infer_degree(field, evaluations, domain_offset):
+    """fft::infer_degree (math/src/fft/mod.rs:540-560): degree of the polynomial interpolating `evaluations` over the
+    coset; 0 for the zero polynomial (polynom::degree_of)."""
+    poly = np.array(_n(field, evaluations), copy=True)
+    interpolate_poly_with_offset(field, poly, None, domain_offset)
+    nz = np.nonzero(poly.reshape(poly.shape[0], -1).any(axis=1))[0]
+    return int(nz[-1]) if len(nz) else 0
+
+
 def permute_index(size, index):
     """fft::permute_index (math/src/fft/mod.rs:592-600)."""
     bits = size.bit_length() - 1

@@ -116,6 +116,48 @@ def test_evaluate_poly_with_offset(wg, oracle, field):
         assert np.array_equal(got, want), (n, blowup)
 
 
+def _one(field):
+    return np.array([0xFFFFFFFF], dtype=np.uint64) if field == F64 else np.array([1, 0], dtype=np.uint64)
+
+
+@pytest.mark.parametrize("field", [F64, F128])
+def test_evaluate_poly_and_serial_fft(wg, oracle, field):
+    """fft::evaluate_poly / serial_fft == evaluation over the unshifted domain (math/src/fft/tests.rs:19-46)."""
+    for n in [2, 4, 32, 1024, 4096, 8192, 1 << 15]:
+        p = rand_cols(field, 300 + n, 1, n)[0]
+        want = oracle.evaluate_poly_with_offset(field, p, _one(field), 1)
+        got = np.ascontiguousarray(p).copy()
+        wg.fft.evaluate_poly(field, got, wg.fft.get_twiddles(field, n) if n <= 32 else None)
+        assert np.array_equal(got, want), n
+        got2 = np.ascontiguousarray(p).copy()
+        wg.fft.serial_fft(field, got2)
+        assert np.array_equal(got2, want), n
+
+
+@pytest.mark.parametrize("field", [F64, F128])
+def test_interpolate_poly_with_offset_and_infer_degree(wg, oracle, field):
+    """interpolate_poly_with_offset inverts evaluation over the coset (math/src/fft/tests.rs:48-60); infer_degree finds
+    the highest non-zero coefficient (fft/mod.rs:524-560)."""
+    gen = wg.matrix.GENERATOR_INTERNAL[field]
+    other = np.array([0x123456789ABCDEF % P64], dtype=np.uint64) if field == F64 else np.array([12345, 678], dtype=np.uint64)
+    for n, off in [(2, gen), (16, other), (1024, gen), (4096, other), (8192, gen), (1 << 14, other)]:
+        p = rand_cols(field, 400 + n, 1, n)[0]
+        evals = oracle.evaluate_poly_with_offset(field, p, off, 1)
+        got = np.ascontiguousarray(evals).copy()
+        wg.fft.interpolate_poly_with_offset(field, got, None, off)
+        assert np.array_equal(got, p), n
+        deg = max(n // 4 - 1, 0)
+        q = np.ascontiguousarray(p).copy()
+        q[deg + 1:] = 0
+        if not q[deg].any():
+            q[deg] = _one(field)
+        ev = oracle.evaluate_poly_with_offset(field, q, off, 1)
+        assert wg.fft.infer_degree(field, ev, off) == deg, n
+    with pytest.raises(wg.WinterGpuError) as e:
+        wg.fft.interpolate_poly_with_offset(F64, np.zeros(8, dtype=np.uint64), None, np.zeros(1, dtype=np.uint64))
+    assert e.value.code == wg._lib.ERR_ZERO_OFFSET
+
+
 @pytest.mark.parametrize("field,cols,n,blowup", [
     (F64, 64, 256, 8),      # prover/src/matrix/tests.rs:14-40
     (F64, 1, 8, 2), (F64, 7, 16, 4), (F64, 9, 64, 8), (F64, 13, 4096, 8), (F64, 100, 1024, 8),
