@@ -108,6 +108,34 @@ int wg_commit_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint3
                     const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
                     void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out);
 
+/* Prover::build_constraint_commitment (prover/src/lib.rs:680-715) = RowMatrix::evaluate_polys_over::<8>(composition_poly
+ * columns, domain) + commit_to_rows: n_cols coefficient columns of n_coeffs elements each (an extension-field composition
+ * polynomial is passed as its base-field columns, col_matrix.rs:113-119). Outputs as for wg_commit_trace, each may be NULL. */
+int wg_commit_polys(int field, int hash, uint64_t n_coeffs, uint64_t blowup, uint32_t n_cols, const void* const* poly_ptrs,
+                    void* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out);
+
+/* ---- resident commitments: the LDE matrices, leaves and tree stay in HBM --------------------------------------------
+ * What the prover needs after committing is the root, then the rows at the query positions with their authentication
+ * paths (TraceCommitment::query -> build_segment_queries -> MerkleTree::prove_batch, prover/src/trace/commitment.rs:
+ * 87-190, crypto/src/merkle/mod.rs:222-284; same for ConstraintCommitment::query, prover/src/constraints/commitment.rs).
+ * A handle owns the device buffers until wg_commitment_free. */
+int wg_commitment_from_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                             const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
+                             uint8_t* root_out, void** handle);
+int wg_commitment_from_polys(int field, int hash, uint64_t n_coeffs, uint64_t blowup, uint32_t n_cols,
+                             const void* const* poly_ptrs, uint8_t* root_out, void** handle);
+/* shape: LDE rows, number of traces, and per trace the real columns and the stored row width (arrays of n_traces) */
+int wg_commitment_info(const void* handle, uint64_t* lde_rows, uint32_t* n_traces, uint32_t* cols_per_trace,
+                       uint32_t* row_widths);
+/* RowMatrix::row(pos) for each position (row_matrix.rs:160-165): rows_out is n_pos x cols_per_trace[trace] elements */
+int wg_commitment_rows(const void* handle, uint32_t trace, uint32_t n_pos, const uint64_t* positions, void* rows_out);
+/* digests by index: which = 0 -> tree.leaves[i], 1 -> tree.nodes[i] (heap layout); out is n x 32 bytes. These are the
+ * reads MerkleTree::prove / prove_batch perform (crypto/src/merkle/mod.rs:194-284). */
+int wg_commitment_digests(const void* handle, int which, uint32_t n, const uint64_t* indexes, uint8_t* out);
+/* full copy to the host (lde_out[t] may be NULL per trace; leaves_out / nodes_out may be NULL) */
+int wg_commitment_download(const void* handle, void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out);
+int wg_commitment_free(void* handle);
+
 /* ---- device-resident entry points (no host transfers; what bench.py's `value` times) -------------------- */
 /* All pointers are device pointers on the wg_init device; `stream` is a cudaStream_t (NULL = default stream).
  * Column matrices are contiguous: element (c, r) at [c*n + r]. */

@@ -20,6 +20,8 @@ SYMBOLS = [
     "wg_interpolate_poly_with_offset", "wg_evaluate_poly", "wg_evaluate_poly_with_offset", "wg_interpolate_columns", "wg_evaluate_polys_over", "wg_hash_rows", "wg_merkle_new",
     "wg_commit_trace", "wg_interpolate_scratch_elems", "wg_lde_scratch_elems", "wg_interpolate_columns_dev",
     "wg_lde_dev", "wg_hash_rows_dev", "wg_merkle_dev", "wg_commit_trace_dev",
+    "wg_commit_polys", "wg_commitment_from_trace", "wg_commitment_from_polys", "wg_commitment_info", "wg_commitment_rows",
+    "wg_commitment_digests", "wg_commitment_download", "wg_commitment_free",
 ]
 
 
@@ -69,6 +71,14 @@ def lib():
         L.wg_hash_rows_dev.argtypes = [i32, i32, u32, vp, vp, vp, u64, vp, vp]
         L.wg_merkle_dev.argtypes = [i32, vp, u64, vp, vp]
         L.wg_commit_trace_dev.argtypes = [i32, i32, u64, u64, u32, vp, vp, vp, vp, vp, vp, vp, u64, vp]
+        L.wg_commit_polys.argtypes = [i32, i32, u64, u64, u32, vp, vp, vp, vp, vp]
+        L.wg_commitment_from_trace.argtypes = [i32, i32, u64, u64, u32, vp, vp, vp, vp, vp]
+        L.wg_commitment_from_polys.argtypes = [i32, i32, u64, u64, u32, vp, vp, vp]
+        L.wg_commitment_info.argtypes = [vp, vp, vp, vp, vp]
+        L.wg_commitment_rows.argtypes = [vp, u32, u32, vp, vp]
+        L.wg_commitment_digests.argtypes = [vp, i32, u32, vp, vp]
+        L.wg_commitment_download.argtypes = [vp, vp, vp, vp]
+        L.wg_commitment_free.argtypes = [vp]
         _lib = L
     return _lib
 

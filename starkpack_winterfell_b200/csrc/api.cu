@@ -52,6 +52,22 @@ static int fail(int code, const char* fmt, ...) {
     if (rc__ != WG_OK) return rc__; \
   } while (0)
 
+// memory the library parks between calls (defined with the commit entry points below)
+static void cache_release_all();
+static void arena_release_if_idle();
+// cudaMalloc that gives parked memory back before reporting failure
+static cudaError_t dev_malloc(void** p, size_t bytes) {
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e == cudaSuccess) return e;
+  cudaGetLastError();
+  cache_release_all();
+  e = cudaMalloc(p, bytes);
+  if (e == cudaSuccess) return e;
+  cudaGetLastError();
+  arena_release_if_idle();
+  return cudaMalloc(p, bytes);
+}
+
 static inline bool is_pow2(uint64_t n) { return n && !(n & (n - 1)); }
 static inline int ilog2(uint64_t n) { return 63 - __builtin_clzll(n); }
 
@@ -603,7 +619,7 @@ struct DevBufFwd {
     if (p) cudaFree(p);
   }
   int alloc(size_t bytes) {
-    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+    cudaError_t e = dev_malloc(&p, bytes ? bytes : 16);
     if (e != cudaSuccess) {
       p = nullptr;
       return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
@@ -708,7 +724,7 @@ struct DevBuf {
   }
   int alloc(size_t bytes) {
     if (bytes == 0) bytes = 16;
-    cudaError_t e = cudaMalloc(&p, bytes);
+    cudaError_t e = dev_malloc(&p, bytes);
     if (e != cudaSuccess) {
       p = nullptr;
       return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
@@ -825,6 +841,13 @@ static cudaStream_t g_s_compute = nullptr, g_s_copy = nullptr, g_s_h2d = nullptr
 static cudaEvent_t g_ev[3] = {nullptr, nullptr, nullptr};
 static cudaEvent_t g_ev_h2d[H2D_CHUNKS];
 
+static void arena_release_if_idle() {
+  if (!g_commit_mu.try_lock()) return;  // a commit is using it
+  if (g_arena) cudaFree(g_arena);
+  g_arena = nullptr;
+  g_arena_bytes = 0;
+  g_commit_mu.unlock();
+}
 static int arena_reserve(size_t bytes) {
   if (!g_s_compute) {
     CUDA_TRY(cudaStreamCreateWithFlags(&g_s_compute, cudaStreamNonBlocking));
@@ -838,7 +861,15 @@ static int arena_reserve(size_t bytes) {
   g_arena = nullptr;
   g_arena_bytes = 0;
   cudaError_t e = cudaMalloc(&g_arena, bytes);
-  if (e != cudaSuccess) return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+  if (e != cudaSuccess) {  // give back parked commitment buffers and retry once
+    cudaGetLastError();
+    cache_release_all();
+    e = cudaMalloc(&g_arena, bytes);
+  }
+  if (e != cudaSuccess) {
+    g_arena = nullptr;
+    return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+  }
   g_arena_bytes = bytes;
   return WG_OK;
 }
@@ -929,6 +960,184 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   return WG_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ resident commitments
+// A commitment whose LDE matrices, leaves and tree stay in HBM: the prover's later steps only need the root, the rows at
+// the ~30-100 query positions and their authentication paths (TraceCommitment::query, prover/src/trace/commitment.rs:
+// 87-190; MerkleTree::prove_batch, crypto/src/merkle/mod.rs:222-284), so the 33 GB D2H of the host-pointer commit is
+// replaced by a few kilobytes. wg_commitment_download() still returns everything for a CPU prover that wants it.
+// Freed commitment buffers are parked here and handed to the next commitment of the same shape: cudaMalloc / cudaFree
+// of a 28 GB matrix cost tens of milliseconds each. wg_shutdown() (or a failed allocation) empties the cache.
+static std::mutex g_cache_mu;
+static std::vector<std::pair<void*, size_t>> g_block_cache;
+static void cache_release_all() {
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  for (auto& b : g_block_cache) cudaFree(b.first);
+  g_block_cache.clear();
+}
+static int cached_malloc(void** p, size_t bytes) {
+  {
+    std::lock_guard<std::mutex> lk(g_cache_mu);
+    for (size_t i = 0; i < g_block_cache.size(); i++)
+      if (g_block_cache[i].second == bytes) {
+        *p = g_block_cache[i].first;
+        g_block_cache.erase(g_block_cache.begin() + i);
+        return WG_OK;
+      }
+  }
+  cudaError_t e = dev_malloc(p, bytes);
+  if (e != cudaSuccess) {
+    *p = nullptr;
+    return fail(WG_ERR_NOMEM, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e));
+  }
+  return WG_OK;
+}
+static void cached_free(void* p, size_t bytes) {
+  if (!p) return;
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  if (g_block_cache.size() >= 2 * HASH_MAX_TRACES + 4) {
+    cudaFree(p);
+    return;
+  }
+  g_block_cache.emplace_back(p, bytes);
+}
+
+struct Commitment {
+  int field = 0, hash = 0;
+  uint64_t n = 0, blowup = 0, L = 0;
+  std::vector<uint32_t> cols;
+  std::vector<uint64_t> rws;
+  std::vector<void*> ldes;
+  uint8_t* leaves = nullptr;
+  uint8_t* nodes = nullptr;
+  size_t lde_bytes(size_t t) const { return L * rws[t] * (field == WG_FIELD_F64 ? 8 : 16); }
+  ~Commitment() {
+    for (size_t t = 0; t < ldes.size(); t++) cached_free(ldes[t], lde_bytes(t));
+    cached_free(leaves, L * 32);
+    cached_free(nodes, L * 32);
+  }
+};
+
+template <class F>
+static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool inputs_are_polys, void* const* polys_out,
+                            uint8_t* root_out) {
+  typedef typename F::T T;
+  const uint64_t n = cm->n, blowup = cm->blowup, L = cm->L;
+  const uint32_t n_traces = (uint32_t)cm->cols.size();
+  WG_TRY(check_domain<F>(n, blowup));
+  if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
+  if (cm->hash != WG_HASH_BLAKE3_256 && cm->hash != WG_HASH_SHA3_256) return fail(WG_ERR_ARG, "unknown hash %d", cm->hash);
+  uint64_t total_cols = 0, max_cols = 0;
+  for (uint32_t c : cm->cols) {
+    if (c == 0) return fail(WG_ERR_ARG, "a trace has no columns");
+    total_cols += c;
+    if (c > max_cols) max_cols = c;
+  }
+  const size_t colb = n * sizeof(T);
+  // persistent buffers
+  auto dmalloc = [&](void** p, size_t bytes) -> int { return cached_malloc(p, bytes); };
+  cm->ldes.assign(n_traces, nullptr);
+  cm->rws.resize(n_traces);
+  for (uint32_t t = 0; t < n_traces; t++) {
+    cm->rws[t] = (uint64_t)(cm->cols[t] + 7) / 8 * 8;
+    WG_TRY(dmalloc(&cm->ldes[t], L * cm->rws[t] * sizeof(T)));
+  }
+  WG_TRY(dmalloc((void**)&cm->leaves, L * 32));
+  WG_TRY(dmalloc((void**)&cm->nodes, L * 32));
+  // temporaries from the shared arena
+  uint64_t se = inputs_are_polys ? 0 : interpolate_scratch_elems<F>((uint32_t)(total_cols < 65535 ? total_cols : 65535), n);
+  // LDE scratch: whole matrix when it fits next to everything else, else 8-column sweeps
+  size_t free_b = 0, total_b = 0;
+  CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
+  auto al = [](size_t b) { return (b + 255) / 256 * 256; };
+  std::lock_guard<std::mutex> lk(g_commit_mu);
+  uint64_t lde_cols = max_cols;
+  const size_t fixed = (inputs_are_polys ? 1 : 2) * al(colb * total_cols) + 4096;
+  while (lde_cols > 8 && fixed + lde_scratch_elems<F>((uint32_t)lde_cols, n, blowup) * sizeof(T) > free_b + g_arena_bytes) lde_cols = (lde_cols / 2 + 7) / 8 * 8;
+  const uint64_t se2 = lde_scratch_elems<F>((uint32_t)lde_cols, n, blowup);
+  if (se2 > se) se = se2;
+  WG_TRY(arena_reserve(fixed + al(se * sizeof(T) + 16)));
+  char* cur = g_arena;
+  auto take = [&](size_t b) {
+    char* r = cur;
+    cur += al(b);
+    return r;
+  };
+  T* polys = (T*)take(colb * total_cols);
+  T* cols = inputs_are_polys ? nullptr : (T*)take(colb * total_cols);
+  T* scr = (T*)take(se * sizeof(T) + 16);
+  cudaStream_t sc = g_s_compute, sx = g_s_copy, sh = g_s_h2d;
+  const uint64_t per = (total_cols + H2D_CHUNKS - 1) / H2D_CHUNKS;
+  for (uint64_t c0 = 0, k = 0; c0 < total_cols; c0 += per, k++) {
+    const uint32_t nc = (uint32_t)((total_cols - c0) < per ? (total_cols - c0) : per);
+    T* dst = inputs_are_polys ? polys : cols;
+    for (uint64_t c = c0; c < c0 + nc; c++)
+      CUDA_TRY(cudaMemcpyAsync((char*)dst + c * colb, column_ptrs[c], colb, cudaMemcpyHostToDevice, sh));
+    CUDA_TRY(cudaEventRecord(g_ev_h2d[k], sh));
+    CUDA_TRY(cudaStreamWaitEvent(sc, g_ev_h2d[k], 0));
+    if (!inputs_are_polys) WG_TRY(interpolate_columns_dev<F>(cols + c0 * n, nc, n, polys + c0 * n, scr, se, sc));
+  }
+  if (polys_out && !inputs_are_polys) {
+    CUDA_TRY(cudaEventRecord(g_ev[0], sc));
+    CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[0], 0));
+    for (uint64_t c = 0; c < total_cols; c++)
+      CUDA_TRY(cudaMemcpyAsync(polys_out[c], (char*)polys + c * colb, colb, cudaMemcpyDeviceToHost, sx));
+  }
+  uint64_t c0 = 0;
+  std::vector<const void*> lde_c(n_traces);
+  std::vector<uint64_t> els(n_traces);
+  for (uint32_t t = 0; t < n_traces; t++) {
+    WG_TRY(lde_dev<F>(polys + c0 * n, cm->cols[t], n, blowup, generator<F>(), (T*)cm->ldes[t], cm->rws[t], scr, se, sc));
+    lde_c[t] = cm->ldes[t];
+    els[t] = cm->cols[t];
+    c0 += cm->cols[t];
+  }
+  WG_TRY(hash_rows_dev<F>(cm->hash, n_traces, lde_c.data(), cm->rws.data(), els.data(), L, cm->leaves, sc));
+  WG_TRY(merkle_dev(cm->hash, cm->leaves, L, cm->nodes, sc));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, cm->nodes + 32, 32, cudaMemcpyDeviceToHost, sc));
+  CUDA_TRY(cudaStreamSynchronize(sc));
+  CUDA_TRY(cudaStreamSynchronize(sx));
+  CUDA_TRY(cudaStreamSynchronize(sh));
+  return WG_OK;
+}
+
+static int commitment_create(int field, int hash, uint64_t n, uint64_t blowup, uint32_t n_traces, const uint32_t* cols_per_trace,
+                             const void* const* column_ptrs, bool inputs_are_polys, void* const* polys_out, uint8_t* root_out,
+                             void** handle) {
+  if (!cols_per_trace || !column_ptrs || !handle) return fail(WG_ERR_ARG, "null pointer");
+  if (field != WG_FIELD_F64 && field != WG_FIELD_F128) return fail(WG_ERR_ARG, "unknown field id %d", field);
+  WG_TRY(ensure_device());
+  Commitment* cm = new Commitment;
+  cm->field = field;
+  cm->hash = hash;
+  cm->n = n;
+  cm->blowup = blowup;
+  cm->L = n * blowup;
+  cm->cols.assign(cols_per_trace, cols_per_trace + n_traces);
+  int rc = field == WG_FIELD_F64 ? commitment_build<Gl64>(cm, column_ptrs, inputs_are_polys, polys_out, root_out)
+                                 : commitment_build<F128>(cm, column_ptrs, inputs_are_polys, polys_out, root_out);
+  if (rc != WG_OK) {
+    delete cm;
+    *handle = nullptr;
+    return rc;
+  }
+  *handle = cm;
+  return WG_OK;
+}
+
+// out[p*elems + e] = lde[pos[p]*rw + e] in 8-byte words
+__global__ void gather_rows_kernel(const uint64_t* lde, uint64_t rw_words, uint32_t elem_words, const uint64_t* pos, uint32_t n_pos,
+                                   uint64_t* out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (uint64_t)n_pos * elem_words) return;
+  const uint32_t p = (uint32_t)(i / elem_words), e = (uint32_t)(i % elem_words);
+  out[i] = lde[pos[p] * rw_words + e];
+}
+__global__ void gather_digests_kernel(const uint4* src, const uint64_t* idx, uint32_t n, uint4* out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * n) return;
+  out[i] = src[2 * idx[i >> 1] + (i & 1)];
+}
+
 }  // namespace wg
 
 // ================================================================================================ extern "C"
@@ -959,7 +1168,15 @@ int wg_init(int device) {
   return WG_OK;
 }
 
-int wg_shutdown(void) { return WG_OK; }  // tables live for the process lifetime
+// releases the transfer arena and parked commitment buffers; twiddle tables live for the process lifetime
+int wg_shutdown(void) {
+  cache_release_all();
+  std::lock_guard<std::mutex> lk(g_commit_mu);
+  if (g_arena) cudaFree(g_arena);
+  g_arena = nullptr;
+  g_arena_bytes = 0;
+  return WG_OK;
+}
 
 const char* wg_last_error(void) { return g_last_error.c_str(); }
 uint64_t wg_launch_count(void) { return g_launches.load(); }
@@ -1090,6 +1307,102 @@ int wg_commit_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint3
                                          leaves_out, nodes_out, root_out),
                     h_commit_trace<F128>(hash, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out,
                                          leaves_out, nodes_out, root_out));
+}
+
+int wg_commit_polys(int field, int hash, uint64_t n_coeffs, uint64_t blowup, uint32_t n_cols, const void* const* poly_ptrs,
+                    void* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out) {
+  void* h = nullptr;
+  WG_TRY(commitment_create(field, hash, n_coeffs, blowup, 1, &n_cols, poly_ptrs, true, nullptr, root_out, &h));
+  void* ldes[1] = {lde_out};
+  int rc = wg_commitment_download(h, ldes, leaves_out, nodes_out);
+  wg_commitment_free(h);
+  return rc;
+}
+
+// ---- resident commitments
+int wg_commitment_from_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                             const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
+                             uint8_t* root_out, void** handle) {
+  return commitment_create(field, hash, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, false, polys_out, root_out, handle);
+}
+
+int wg_commitment_from_polys(int field, int hash, uint64_t n_coeffs, uint64_t blowup, uint32_t n_cols, const void* const* poly_ptrs,
+                             uint8_t* root_out, void** handle) {
+  return commitment_create(field, hash, n_coeffs, blowup, 1, &n_cols, poly_ptrs, true, nullptr, root_out, handle);
+}
+
+int wg_commitment_rows(const void* handle, uint32_t trace, uint32_t n_pos, const uint64_t* positions, void* rows_out) {
+  const Commitment* cm = (const Commitment*)handle;
+  if (!cm || !positions || !rows_out) return fail(WG_ERR_ARG, "null pointer");
+  if (trace >= cm->cols.size()) return fail(WG_ERR_ARG, "trace index %u out of range", trace);
+  if (n_pos == 0) return WG_OK;
+  for (uint32_t i = 0; i < n_pos; i++)
+    if (positions[i] >= cm->L) return fail(WG_ERR_ARG, "position %llu out of range (%llu rows)", (unsigned long long)positions[i], (unsigned long long)cm->L);
+  WG_TRY(ensure_device());
+  const uint32_t w = cm->field == WG_FIELD_F64 ? 1 : 2;
+  const uint32_t ew = cm->cols[trace] * w;
+  DevBuf dpos, dout;
+  WG_TRY(dpos.alloc(n_pos * 8));
+  WG_TRY(dout.alloc((size_t)n_pos * ew * 8));
+  CUDA_TRY(cudaMemcpyAsync(dpos.p, positions, n_pos * 8, cudaMemcpyHostToDevice, 0));
+  gather_rows_kernel<<<cdiv((uint64_t)n_pos * ew, 256), 256, 0, 0>>>((const uint64_t*)cm->ldes[trace], cm->rws[trace] * w, ew,
+                                                                   dpos.as<uint64_t>(), n_pos, dout.as<uint64_t>());
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  CUDA_TRY(cudaMemcpyAsync(rows_out, dout.p, (size_t)n_pos * ew * 8, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_commitment_digests(const void* handle, int which, uint32_t n, const uint64_t* indexes, uint8_t* out) {
+  const Commitment* cm = (const Commitment*)handle;
+  if (!cm || !indexes || !out) return fail(WG_ERR_ARG, "null pointer");
+  if (which != 0 && which != 1) return fail(WG_ERR_ARG, "which must be 0 (leaves) or 1 (nodes)");
+  if (n == 0) return WG_OK;
+  for (uint32_t i = 0; i < n; i++)
+    if (indexes[i] >= cm->L) return fail(WG_ERR_ARG, "index %llu out of range (%llu digests)", (unsigned long long)indexes[i], (unsigned long long)cm->L);
+  WG_TRY(ensure_device());
+  DevBuf didx, dout;
+  WG_TRY(didx.alloc(n * 8));
+  WG_TRY(dout.alloc((size_t)n * 32));
+  CUDA_TRY(cudaMemcpyAsync(didx.p, indexes, n * 8, cudaMemcpyHostToDevice, 0));
+  gather_digests_kernel<<<cdiv(2 * (uint64_t)n, 256), 256, 0, 0>>>((const uint4*)(which ? cm->nodes : cm->leaves), didx.as<uint64_t>(), n,
+                                                                  dout.as<uint4>());
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  CUDA_TRY(cudaMemcpyAsync(out, dout.p, (size_t)n * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_commitment_info(const void* handle, uint64_t* lde_rows, uint32_t* n_traces, uint32_t* cols_per_trace, uint32_t* row_widths) {
+  const Commitment* cm = (const Commitment*)handle;
+  if (!cm) return fail(WG_ERR_ARG, "null handle");
+  if (lde_rows) *lde_rows = cm->L;
+  if (n_traces) *n_traces = (uint32_t)cm->cols.size();
+  for (size_t t = 0; t < cm->cols.size(); t++) {
+    if (cols_per_trace) cols_per_trace[t] = cm->cols[t];
+    if (row_widths) row_widths[t] = (uint32_t)cm->rws[t];
+  }
+  return WG_OK;
+}
+
+int wg_commitment_download(const void* handle, void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out) {
+  const Commitment* cm = (const Commitment*)handle;
+  if (!cm) return fail(WG_ERR_ARG, "null handle");
+  WG_TRY(ensure_device());
+  const size_t es = cm->field == WG_FIELD_F64 ? 8 : 16;
+  for (size_t t = 0; lde_out && t < cm->cols.size(); t++)
+    if (lde_out[t]) CUDA_TRY(cudaMemcpyAsync(lde_out[t], cm->ldes[t], cm->L * cm->rws[t] * es, cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, cm->leaves, cm->L * 32, cudaMemcpyDeviceToHost, 0));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, cm->nodes, cm->L * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_commitment_free(void* handle) {
+  delete (Commitment*)handle;
+  return WG_OK;
 }
 
 // ---- device-resident

@@ -6,7 +6,7 @@ import numpy as np
 
 from ._lib import F64, F128, check, lib
 from .matrix import ColMatrix, RowMatrix, StarkDomain, _ptr_array
-from .merkle import MerkleTree
+from .merkle import MerkleTree, MerkleTreeError, _DigestPlan, _DigestTable, _prove, _prove_batch
 
 
 class TraceCommitment:
@@ -49,3 +49,135 @@ def build_trace_commitment(hash_id, traces, domain, want_lde=True, want_polys=Tr
     lde_m = [RowMatrix(f, d, d.shape[1], t.num_cols()) for d, t in zip(ldes, traces)] if ldes else []
     poly_m = [ColMatrix(f, p) for p in polys] if polys else []
     return lde_m, tree, poly_m
+
+
+def build_constraint_commitment(hash_id, composition_poly, domain):
+    """Prover::build_constraint_commitment (prover/src/lib.rs:680-715): evaluate the composition polynomial columns
+    (a ColMatrix of coefficients) over the LDE domain and commit to the rows. Returns (RowMatrix, MerkleTree), the two
+    members of ConstraintCommitment (prover/src/constraints/commitment.rs)."""
+    f = composition_poly.field
+    n, B = composition_poly.num_rows(), domain.blowup
+    L = n * B
+    rw = (composition_poly.num_cols() + 7) // 8 * 8
+    lde = np.empty((L, rw) if f == F64 else (L, rw, 2), dtype=np.uint64)
+    leaves = np.empty((L, 32), dtype=np.uint8)
+    nodes = np.empty((L, 32), dtype=np.uint8)
+    root = np.empty(32, dtype=np.uint8)
+    check(lib().wg_commit_polys(f, hash_id, n, B, composition_poly.num_cols(), _ptr_array(composition_poly.columns),
+                                C.c_void_p(lde.ctypes.data), C.c_void_p(leaves.ctypes.data), C.c_void_p(nodes.ctypes.data),
+                                C.c_void_p(root.ctypes.data)))
+    return RowMatrix(f, lde, rw, composition_poly.num_cols()), MerkleTree.from_raw_parts(hash_id, nodes, leaves)
+
+
+class JointTraceQueries:
+    """prover/src/trace/commitment.rs build_segment_queries: the batch proof, the concatenated rows ("comb_states") and
+    the per-trace rows at the queried positions."""
+
+    def __init__(self, trace_proof, comb_states, traces_states):
+        self.trace_proof, self.comb_states, self.traces_states = trace_proof, comb_states, traces_states
+
+
+class ResidentCommitment:
+    """A trace (or constraint) commitment whose LDE matrices and Merkle tree stay in HBM. `query(positions)` is
+    TraceCommitment::query (prover/src/trace/commitment.rs:87-116): only the queried rows and the digests
+    MerkleTree::prove_batch reads cross PCIe."""
+
+    def __init__(self, field, hash_id, handle, root, polys):
+        self.field, self.hash_id, self._h, self._root, self.polys = field, hash_id, handle, root, polys
+        L, nt = C.c_uint64(), C.c_uint32()
+        check(lib().wg_commitment_info(self._h, C.byref(L), C.byref(nt), None, None))
+        cpt, rws = (C.c_uint32 * nt.value)(), (C.c_uint32 * nt.value)()
+        check(lib().wg_commitment_info(self._h, None, None, cpt, rws))
+        self.lde_rows, self.cols_per_trace, self.row_widths = L.value, list(cpt), list(rws)
+
+    @classmethod
+    def from_traces(cls, hash_id, traces, domain, want_polys=True, polys_out=None):
+        """polys_out: optional preallocated arrays (e.g. pinned memory), one list per trace, that receive the polys."""
+        f = traces[0].field
+        n = traces[0].num_rows()
+        assert all(t.num_rows() == n and t.field == f for t in traces)
+        cols = [c for t in traces for c in t.columns]
+        cpt = (C.c_uint32 * len(traces))(*[t.num_cols() for t in traces])
+        polys = None
+        if polys_out is not None:
+            polys = polys_out
+        elif want_polys:
+            polys = [[np.empty_like(c) for c in t.columns] for t in traces]
+        root = np.empty(32, dtype=np.uint8)
+        h = C.c_void_p()
+        check(lib().wg_commitment_from_trace(f, hash_id, n, domain.blowup, len(traces), cpt, _ptr_array(cols),
+                                             _ptr_array([c for p in polys for c in p]) if polys else None,
+                                             C.c_void_p(root.ctypes.data), C.byref(h)))
+        return cls(f, hash_id, h, bytes(root), [ColMatrix(f, p) for p in polys] if polys else [])
+
+    @classmethod
+    def from_polys(cls, hash_id, composition_poly, domain):
+        f = composition_poly.field
+        root = np.empty(32, dtype=np.uint8)
+        h = C.c_void_p()
+        check(lib().wg_commitment_from_polys(f, hash_id, composition_poly.num_rows(), domain.blowup, composition_poly.num_cols(),
+                                             _ptr_array(composition_poly.columns), C.c_void_p(root.ctypes.data), C.byref(h)))
+        return cls(f, hash_id, h, bytes(root), [])
+
+    def root(self):
+        return self._root
+
+    def depth(self):
+        return self.lde_rows.bit_length() - 1
+
+    def rows(self, trace, positions):
+        """RowMatrix::row for each position: [n_pos, cols] (f64) / [n_pos, cols, 2] (f128)."""
+        pos = np.ascontiguousarray(positions, dtype=np.uint64)
+        c = self.cols_per_trace[trace]
+        out = np.empty((len(pos), c) if self.field == F64 else (len(pos), c, 2), dtype=np.uint64)
+        check(lib().wg_commitment_rows(self._h, trace, len(pos), C.c_void_p(pos.ctypes.data), C.c_void_p(out.ctypes.data)))
+        return out
+
+    def _digests(self, which, idx):
+        idx = np.ascontiguousarray(idx, dtype=np.uint64)
+        out = np.empty((len(idx), 32), dtype=np.uint8)
+        if len(idx):
+            check(lib().wg_commitment_digests(self._h, which, len(idx), C.c_void_p(idx.ctypes.data), C.c_void_p(out.ctypes.data)))
+        return out
+
+    def _with_digests(self, fn):
+        plan = _DigestPlan()
+        fn(plan)  # raises the reference's errors before touching the device
+        table = _DigestTable(plan.leaf_idx, self._digests(0, plan.leaf_idx), plan.node_idx, self._digests(1, plan.node_idx))
+        return fn(table)
+
+    def prove(self, index):
+        return self._with_digests(lambda src: _prove(src, self.lde_rows, int(index)))
+
+    def prove_batch(self, indexes):
+        return self._with_digests(lambda src: _prove_batch(src, self.lde_rows, self.depth(), indexes))
+
+    def query(self, positions):
+        traces_states = [self.rows(t, positions) for t in range(len(self.cols_per_trace))]
+        comb_states = np.concatenate(traces_states, axis=1)
+        return JointTraceQueries(self.prove_batch(positions), comb_states, traces_states)
+
+    def download(self, want_lde=True):
+        """-> (list[RowMatrix], MerkleTree): the full host copy build_trace_commitment returns."""
+        L = self.lde_rows
+        ldes = []
+        if want_lde:
+            for rw in self.row_widths:
+                ldes.append(np.empty((L, rw) if self.field == F64 else (L, rw, 2), dtype=np.uint64))
+        leaves = np.empty((L, 32), dtype=np.uint8)
+        nodes = np.empty((L, 32), dtype=np.uint8)
+        check(lib().wg_commitment_download(self._h, _ptr_array(ldes) if ldes else None, C.c_void_p(leaves.ctypes.data),
+                                           C.c_void_p(nodes.ctypes.data)))
+        mats = [RowMatrix(self.field, d, d.shape[1], c) for d, c in zip(ldes, self.cols_per_trace)]
+        return mats, MerkleTree.from_raw_parts(self.hash_id, nodes, leaves)
+
+    def close(self):
+        if self._h:
+            lib().wg_commitment_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
