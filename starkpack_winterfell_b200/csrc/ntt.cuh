@@ -180,7 +180,7 @@ __device__ __forceinline__ typename F::T table2(const typename F::T* __restrict_
 template <class F, int LOG_S, int LAYOUT, bool INV, int U>
 __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* tile, const typename F::T* tws,
                                           const typename F::T* qtab, long long in_base, long long out_base, uint32_t w0,
-                                          uint32_t y, uint32_t z) {
+                                          uint32_t y, uint32_t z, bool tws_sync = false) {
   typedef typename F::T T;
   typedef PassCfg<F, LOG_S, LAYOUT> C;
   constexpr int LR = C::lr(U);
@@ -243,6 +243,10 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
     radix_ntt<F, LR, INV>(a);
 
     if (!LAST) {
+      // The block's first step 0 runs while the shared twiddle table is still being filled (its loads overlap the
+      // tile loads and the first butterflies); everyone's table stores must have landed before the first read.
+      // Every thread runs the same number of item iterations, so the barrier is uniform.
+      if (FIRST && tws_sync && item == (int)threadIdx.x) __syncthreads();
       // twiddle w_{2^LOGPP}^(m_rest*j) from this step's [j][m_rest] sub-table; then scatter digit j
 #pragma unroll
       for (int j = 0; j < R; j++) {
@@ -315,6 +319,7 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
     gx /= A.zfast;
   }
   const uint32_t nx = A.nx ? A.nx : gx, ny = A.ny ? A.ny : gridDim.y;
+  bool tws_ready = false;  // becomes true at the first barrier after the table load above
   for (uint32_t y = blockIdx.y; y < ny; y += gridDim.y) {
     if (LAYOUT == 1 && A.has_q) {
       // qtab[i] = q^i by doubling: level k appends q^(2^k) * qtab[0 .. 2^k)
@@ -329,6 +334,7 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
         qp = F::mul(qp, qp);
         __syncthreads();
       }
+      tws_ready = true;
     }
     const long long in_base = (long long)y * A.in_ystride + (long long)z * A.in_zstride;
     const long long out_base = (long long)y * A.out_ystride + (long long)z * A.out_zstride;
@@ -342,7 +348,8 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
         }
         continue;
       }
-      pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, qtab, in_base, out_base, w0, y, z);
+      pass_step<F, LOG_S, LAYOUT, INV, 0>(A, tile, tws, qtab, in_base, out_base, w0, y, z, !tws_ready);
+      tws_ready = true;
       if (C::NSTEPS > 1) {
         __syncthreads();
         pass_step<F, LOG_S, LAYOUT, INV, (C::NSTEPS > 1 ? 1 : 0)>(A, tile, tws, qtab, in_base, out_base, w0, y, z);

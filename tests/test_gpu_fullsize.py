@@ -108,3 +108,25 @@ def test_f128_configs_full_size_vs_oracle(oracle, name, hash_id, traces):
     assert np.array_equal(tc.nodes.cpu().numpy(), want["nodes"])
     for t in range(len(trs)):
         assert np.array_equal(tc.ldes[t].cpu().numpy().view(np.uint64), want["lde"][t])
+
+
+@pytest.mark.parametrize("field,log_n,cols,blowup", [
+    (0, 13, 9, 8), (0, 15, 3, 2), (0, 17, 5, 8), (0, 18, 2, 4), (0, 19, 9, 8), (0, 20, 3, 8), (0, 21, 2, 8), (0, 23, 2, 8),
+    (0, 24, 1, 8),   # largest supported transform: both passes 2^12 points (no q table: two-level twiddle path)
+    (1, 17, 2, 8), (1, 19, 3, 4), (1, 21, 1, 8), (1, 22, 1, 2),
+])
+def test_every_two_pass_length_vs_oracle(oracle, field, log_n, cols, blowup):
+    """One commit per transform length so that every (S_strided, S_contiguous) kernel pair the planner can pick is
+    compared with the oracle: polys, LDE words, leaves, nodes."""
+    n = 1 << log_n
+    tr = fx.synth_f64(0xA000 + log_n, cols, n) if field == 0 else fx.synth_f128(0xA000 + log_n, cols, n)
+    tc = _committer(field, 0, n, blowup, [cols])
+    tc.cols.copy_(torch.from_numpy(np.ascontiguousarray(tr).view(np.int64).reshape(tc.cols.shape)).to(tc.device))
+    tc.commit()
+    torch.cuda.synchronize()
+    want = oracle.commit_trace(field, 0, [tr], blowup)
+    assert np.array_equal(tc.polys.cpu().numpy().view(np.uint64).reshape(np.stack(want["polys"][0]).shape), np.stack(want["polys"][0]))
+    assert np.array_equal(tc.ldes[0].cpu().numpy().view(np.uint64).reshape(want["lde"][0].shape), want["lde"][0])
+    assert np.array_equal(tc.leaves.cpu().numpy(), want["leaves"])
+    assert np.array_equal(tc.nodes.cpu().numpy(), want["nodes"])
+    assert tc.root() == bytes(want["root"])
