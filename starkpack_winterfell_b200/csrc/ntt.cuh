@@ -192,6 +192,8 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
   constexpr bool W_FASTEST = (LAYOUT == 0) || (LAST && !FIRST);
   constexpr int NITEMS = (1 << LOGQ) * C::TW;
 
+  // fewer items than threads (tiny transforms): some threads never enter the loop, so the table barrier goes here
+  if (FIRST && !LAST && tws_sync && NITEMS < C::NT) __syncthreads();
   for (int item = threadIdx.x; item < NITEMS; item += C::NT) {
     int q, w;
     if (W_FASTEST) {
@@ -245,8 +247,8 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
     if (!LAST) {
       // The block's first step 0 runs while the shared twiddle table is still being filled (its loads overlap the
       // tile loads and the first butterflies); everyone's table stores must have landed before the first read.
-      // Every thread runs the same number of item iterations, so the barrier is uniform.
-      if (FIRST && tws_sync && item == (int)threadIdx.x) __syncthreads();
+      // With NITEMS >= NT every thread runs the same number of item iterations, so the barrier is uniform.
+      if (FIRST && tws_sync && NITEMS >= C::NT && item == (int)threadIdx.x) __syncthreads();
       // twiddle w_{2^LOGPP}^(m_rest*j) from this step's [j][m_rest] sub-table; then scatter digit j
 #pragma unroll
       for (int j = 0; j < R; j++) {
