@@ -368,7 +368,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-log-rows", type=int, default=18, help="rows (log2) of the CPU baseline sample")
+    ap.add_argument("--cpu-log-rows", type=int, default=20, help="rows (log2) of the CPU baseline sample (2^20: ~10 s)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

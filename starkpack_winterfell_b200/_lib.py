@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libwinter_gpu.so")
+LIB_PATH = os.environ.get("WG_LIB_PATH") or os.path.join(_HERE, "libwinter_gpu.so")  # override: kernel-variant experiments
 
 F64, F128 = 0, 1
 BLAKE3_256, SHA3_256 = 0, 1
