@@ -129,6 +129,13 @@ def cpu_commit_sample(log_rows_sample, steps=1, warmup=0):
             "sample_ms": ms_sample, "sample_root": root.hex()}
 
 
+def workload_config():
+    """`config` of the JSON line, identical in both arms."""
+    return {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit, one trace per GPU",
+            "l2": "inputs (3.4 GB trace, 27 GB LDE) far exceed the 126 MB L2; no flush needed",
+            "value_is": "ms per committed trace = ms_per_step / n_gpus"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -137,8 +144,9 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "ms", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["sample_ms"], "higher_is_better": False,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit",
-                       "reference_arm": "CPU oracle port of the reference's concurrent path (Rust toolchain absent)"},
+            "config": workload_config(),
+            "reference_arm": "CPU oracle port of the reference's concurrent path on the host cores (Rust toolchain absent); one "
+                             "trace, bounded sample scaled linearly in rows",
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -341,9 +349,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": ms / world, "unit": "ms", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms,
         "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit, "
-                               f"one trace per GPU", "l2": "inputs (3.4 GB trace, 27 GB LDE) far exceed the 126 MB L2; no flush needed",
-                   "value_is": "ms per committed trace = ms_per_step / n_gpus"},
+        "config": workload_config(),
         "lde_rows_per_s": world * L / (ms * 1e-3), "trace_rows_per_s": world * n / (ms * 1e-3),
         "commit_roofline": {"algorithmic_bytes": alg, "achieved_gbs": alg / (ms * 1e-3) / 1e9, "frac": alg / (ms * 1e-3) / 1e9 / peak},
         "clocks": clocks, "e2e": e2e, "e2e_resident": e2e_res, "gpu_launches": int(launches), "root": root_hex,
