@@ -136,6 +136,21 @@ int wg_commitment_digests(const void* handle, int which, uint32_t n, const uint6
 int wg_commitment_download(const void* handle, void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out);
 int wg_commitment_free(void* handle);
 
+/* ---- FRI layer commitments (base field, E = B) --------------------------------------------------
+ * wg_fri_commit_layer replaces the first half of FriProver::build_layer (fri/src/prover/mod.rs:185-199):
+ *   transposed = transpose_slice::<E, N>(evaluations)   (utils/core/src/lib.rs:206-225: row i = evals[i + j*rows], j < N)
+ *   leaves     = hash_values::<H, E, N>(&transposed)    (fri/src/utils.rs: hash_elements of each row)
+ *   tree       = MerkleTree::new(leaves)                (crypto/src/merkle/mod.rs:117-136)
+ * n = evaluations.len(), folding_factor N in {2,4,8,16} (prover/mod.rs:178-184, anything else: WG_ERR_UNSUPPORTED).
+ * transposed_out (n elements, the FriLayer's stored evaluations) and leaves_out (n/N x 32) may be NULL;
+ * nodes_out is n/N x 32 bytes in heap layout, root = nodes_out[32..64).
+ * wg_fri_apply_drp replaces folding::apply_drp (fri/src/folding/mod.rs:115-146): out[i] = the degree-respecting
+ * projection of row i at alpha over the coset with offset domain_offset (elements in the internal representation). */
+int wg_fri_commit_layer(int field, int hash, const void* evaluations, uint64_t n, uint32_t folding_factor, void* transposed_out,
+                        uint8_t* leaves_out, uint8_t* nodes_out);
+int wg_fri_apply_drp(int field, const void* transposed, uint64_t rows, uint32_t folding_factor, const void* domain_offset,
+                     const void* alpha, void* out);
+
 /* ---- device-resident entry points (no host transfers; what bench.py's `value` times) -------------------- */
 /* All pointers are device pointers on the wg_init device; `stream` is a cudaStream_t (NULL = default stream).
  * Column matrices are contiguous: element (c, r) at [c*n + r]. */
@@ -159,6 +174,13 @@ int wg_merkle_dev(int hash, const void* d_leaves, uint64_t n_leaves, void* d_nod
 int wg_commit_trace_dev(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
                         const uint32_t* cols_per_trace, const void* d_cols, void* d_polys, void* const* d_ldes,
                         void* d_leaves, void* d_nodes, void* d_scratch, uint64_t scratch_elems, void* stream);
+
+/* FRI layer on device buffers: d_evaluations n elements -> d_transposed n elements, d_leaves / d_nodes (n/N) x 32 bytes;
+ * fold: d_transposed rows x N -> d_out rows elements (the next layer's evaluations). offset and alpha are host elements. */
+int wg_fri_commit_layer_dev(int field, int hash, const void* d_evaluations, uint64_t n, uint32_t folding_factor,
+                            void* d_transposed, void* d_leaves, void* d_nodes, void* stream);
+int wg_fri_apply_drp_dev(int field, const void* d_transposed, uint64_t rows, uint32_t folding_factor,
+                         const void* domain_offset_host, const void* alpha_host, void* d_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -164,3 +164,30 @@ def hash_comb_rows(field, hash_id, mats, elems):
     rc = lib().or_hash_comb_rows(field, hash_id, C.c_uint32(k), ptrs, rws, els, C.c_uint64(rows), _p(leaves))
     assert rc == 0
     return leaves
+
+
+def fri_commit_layer(field, hash_id, evals, folding):
+    """FriProver::build_layer first half (fri/src/prover/mod.rs:185-199) -> dict(transposed, leaves, nodes, root)."""
+    e = np.ascontiguousarray(evals, dtype=np.uint64)
+    n = e.shape[0]
+    rows = n // folding
+    tr = np.empty_like(e)
+    leaves = np.empty((rows, 32), dtype=np.uint8)
+    nodes = np.empty((rows, 32), dtype=np.uint8)
+    rc = lib().or_fri_commit_layer(field, hash_id, _p(e), C.c_uint64(n), C.c_uint32(folding), _p(tr), _p(leaves), _p(nodes))
+    if rc:
+        raise ValueError(f"or_fri_commit_layer rc={rc}")
+    shape = (rows, folding) if field == F64 else (rows, folding, 2)
+    return dict(transposed=tr.reshape(shape), leaves=leaves, nodes=nodes, root=bytes(nodes[1]))
+
+
+def fri_apply_drp(field, transposed, folding, offset, alpha):
+    """folding::apply_drp (fri/src/folding/mod.rs:115-146); transposed [rows, folding(,2)] -> [rows(,2)]."""
+    t = np.ascontiguousarray(transposed, dtype=np.uint64)
+    rows = t.shape[0]
+    out = elems(field, rows)
+    rc = lib().or_fri_apply_drp(field, _p(t), C.c_uint64(rows), C.c_uint32(folding),
+                                _p(np.ascontiguousarray(offset, dtype=np.uint64)), _p(np.ascontiguousarray(alpha, dtype=np.uint64)), _p(out))
+    if rc:
+        raise ValueError(f"or_fri_apply_drp rc={rc}")
+    return out

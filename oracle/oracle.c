@@ -392,3 +392,97 @@ int or_commit_trace(int field, int hash, uint64_t n, uint64_t blowup, uint32_t n
   free(tw);
   return rc;
 }
+
+/* ================================================================================================ FRI layers
+ * (SURVEY 8(f) rank 3). Base field (E = B). */
+
+/* ---- FriProver::build_layer, first half (fri/src/prover/mod.rs:185-199):
+ *   transpose_slice::<E, N> (utils/core/src/lib.rs:206-225): result[i][j] = source[i + j * row_count]
+ *   hash_values::<H, E, N> (fri/src/utils.rs): leaf_i = H::hash_elements(&values[i])
+ *   MerkleTree::new(leaves) */
+int or_fri_commit_layer(int field, int hash, const void* evals, uint64_t n, uint32_t ff, void* transposed_out,
+                        uint8_t* leaves_out, uint8_t* nodes_out) {
+  if (ff != 2 && ff != 4 && ff != 8 && ff != 16) return OR_ERR_ARG;
+  if (n == 0 || n % ff) return OR_ERR_ARG;
+  uint64_t rows = n / ff;
+  size_t es = esize(field);
+  uint8_t* tr = (uint8_t*)transposed_out;
+  uint8_t* tmp = NULL;
+  if (!tr) tr = tmp = (uint8_t*)malloc(n * es);
+  const uint8_t* src = (const uint8_t*)evals;
+  for (uint64_t i = 0; i < rows; i++)
+    for (uint32_t j = 0; j < ff; j++) memcpy(tr + (i * ff + j) * es, src + (i + (uint64_t)j * rows) * es, es);
+  uint8_t* leaves = leaves_out ? leaves_out : (uint8_t*)malloc(rows * 32);
+  uint64_t rw = ff;
+  int rc = or_hash_rows(field, hash, tr, rows, rw, rw, leaves);
+  if (rc == OR_OK) rc = or_merkle_nodes(hash, leaves, rows, nodes_out);
+  if (!leaves_out) free(leaves);
+  free(tmp);
+  return rc;
+}
+
+/* ---- folding::apply_drp (fri/src/folding/mod.rs:115-146) with get_inv_offsets (:186-193):
+ *   inv_offsets = get_power_series_with_offset(g^-1, domain_offset^-1, rows), g = root of unity of order rows * N
+ *   per row: poly = row; serial_fft(poly, get_inv_twiddles(N)) (= fft_in_place + permute, math/src/fft/mod.rs:416-440);
+ *            coeff_k *= (1/N) * inv_offset_i^k; result_i = polynom::eval(poly, alpha) (Horner from the top coefficient) */
+int or_fri_apply_drp(int field, const void* transposed, uint64_t rows, uint32_t ff, const void* domain_offset,
+                     const void* alpha, void* out) {
+  if (ff != 2 && ff != 4 && ff != 8 && ff != 16) return OR_ERR_ARG;
+  if (rows == 0) return OR_OK;
+  if (!is_pow2(rows)) return OR_ERR_NOT_POW2;
+  unsigned log_n = ilog2(rows * ff);
+  if (log_n > (unsigned)(field == 0 ? F64_TWO_ADICITY : F128_TWO_ADICITY)) return OR_ERR_TOO_LARGE;
+  if (field == 0) {
+    uint64_t inv_tw[8];
+    or_get_twiddles(0, ff, 1, inv_tw);
+    uint64_t g_inv = f64_inv(f64_root_of_unity(log_n));
+    uint64_t off_inv = f64_inv(*(const uint64_t*)domain_offset), a = *(const uint64_t*)alpha;
+    uint64_t len_offset = f64_inv(f64_new(ff));
+    const uint64_t* v = (const uint64_t*)transposed;
+    uint64_t* res = (uint64_t*)out;
+    uint64_t s = off_inv; /* inv_offsets[i] */
+    for (uint64_t i = 0; i < rows; i++) {
+      uint64_t poly[16];
+      memcpy(poly, v + i * ff, ff * 8);
+      f64_fft_in_place(poly, ff, 1, inv_tw);
+      f64_permute(poly, ff, 1);
+      uint64_t offset = len_offset;
+      for (uint32_t k = 0; k < ff; k++) {
+        poly[k] = f64_mul(poly[k], offset);
+        offset = f64_mul(offset, s);
+      }
+      uint64_t acc = 0;
+      for (int k = (int)ff - 1; k >= 0; k--) acc = f64_add(f64_mul(acc, a), poly[k]);
+      res[i] = acc;
+      s = f64_mul(s, g_inv);
+    }
+  } else {
+    u128 inv_tw[8];
+    or_get_twiddles(1, ff, 1, inv_tw);
+    u128 g_inv = f128_inv(f128_root_of_unity(log_n));
+    u128 off, a;
+    memcpy(&off, domain_offset, 16);
+    memcpy(&a, alpha, 16);
+    u128 off_inv = f128_inv(off);
+    u128 len_offset = f128_inv((u128)ff);
+    const u128* v = (const u128*)transposed;
+    u128* res = (u128*)out;
+    u128 s = off_inv;
+    for (uint64_t i = 0; i < rows; i++) {
+      u128 poly[16];
+      memcpy(poly, v + i * ff, ff * 16);
+      f128_fft_in_place(poly, ff, 1, inv_tw);
+      f128_permute(poly, ff, 1);
+      u128 offset = len_offset;
+      for (uint32_t k = 0; k < ff; k++) {
+        poly[k] = f128_mul(poly[k], offset);
+        offset = f128_mul(offset, s);
+      }
+      u128 acc = 0;
+      for (int k = (int)ff - 1; k >= 0; k--) acc = f128_add(f128_mul(acc, a), poly[k]);
+      res[i] = acc;
+      s = f128_mul(s, g_inv);
+    }
+  }
+  return OR_OK;
+}

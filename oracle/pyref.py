@@ -139,3 +139,27 @@ def commit(field, hash_id, traces, blowup):
         data = b"".join(elem_bytes(field, col[k]) for tl in ldes for col in tl)
         leaves.append(hash_bytes(hash_id, data))
     return polys, ldes, leaves, merkle_nodes(hash_id, leaves)
+
+
+def fri_fold(field, evals, folding, offset, alpha):
+    """Definition of the degree-respecting projection (what fri/src/folding/mod.rs:115-146 computes): for every i < n/N
+    the polynomial of degree < N through the N points (x_j, evals[i + j*n/N]), x_j = offset * g^(i + j*n/N), evaluated
+    at alpha. Canonical ints in, canonical ints out. O(n*N^2) Lagrange form, independent of any FFT."""
+    p = MOD[field]
+    n = len(evals)
+    rows = n // folding
+    g = root_of_unity(field, n.bit_length() - 1)
+    out = []
+    for i in range(rows):
+        xs = [offset * pow(g, i + j * rows, p) % p for j in range(folding)]
+        ys = [evals[i + j * rows] for j in range(folding)]
+        acc = 0
+        for j in range(folding):
+            num, den = 1, 1
+            for m in range(folding):
+                if m != j:
+                    num = num * (alpha - xs[m]) % p
+                    den = den * (xs[j] - xs[m]) % p
+            acc = (acc + ys[j] * num * pow(den, -1, p)) % p
+        out.append(acc)
+    return out

@@ -22,6 +22,7 @@ SYMBOLS = [
     "wg_lde_dev", "wg_hash_rows_dev", "wg_merkle_dev", "wg_commit_trace_dev",
     "wg_commit_polys", "wg_commitment_from_trace", "wg_commitment_from_polys", "wg_commitment_info", "wg_commitment_rows",
     "wg_commitment_digests", "wg_commitment_download", "wg_commitment_free",
+    "wg_fri_commit_layer", "wg_fri_apply_drp", "wg_fri_commit_layer_dev", "wg_fri_apply_drp_dev",
 ]
 
 
@@ -79,6 +80,10 @@ def lib():
         L.wg_commitment_digests.argtypes = [vp, i32, u32, vp, vp]
         L.wg_commitment_download.argtypes = [vp, vp, vp, vp]
         L.wg_commitment_free.argtypes = [vp]
+        L.wg_fri_commit_layer.argtypes = [i32, i32, vp, u64, u32, vp, vp, vp]
+        L.wg_fri_apply_drp.argtypes = [i32, vp, u64, u32, vp, vp, vp]
+        L.wg_fri_commit_layer_dev.argtypes = [i32, i32, vp, u64, u32, vp, vp, vp, vp]
+        L.wg_fri_apply_drp_dev.argtypes = [i32, vp, u64, u32, vp, vp, vp, vp]
         _lib = L
     return _lib
 

@@ -23,6 +23,7 @@
 #include "hash.cuh"
 #include "hash_kernels.cuh"
 #include "ntt_launch.cuh"
+#include "fri.cuh"
 
 namespace wg {
 
@@ -1138,6 +1139,112 @@ __global__ void gather_digests_kernel(const uint4* src, const uint64_t* idx, uin
   out[i] = src[2 * idx[i >> 1] + (i & 1)];
 }
 
+// ------------------------------------------------------------------------------------------------ FRI layers
+// FriProver::build_layer (fri/src/prover/mod.rs:185-211): transpose_slice -> hash_values -> MerkleTree::new, then
+// folding::apply_drp (fri/src/folding/mod.rs:115-146). Base field only.
+static inline bool fri_folding_ok(uint32_t ff) { return ff == 2 || ff == 4 || ff == 8 || ff == 16; }
+
+template <class F>
+static bool elem_is_canonical(const typename F::T& v);
+template <>
+bool elem_is_canonical<Gl64>(const uint64_t& v) { return v < Gl64::P; }
+template <>
+bool elem_is_canonical<F128>(const u128& v) { return u128_lt(v, F128::modulus()); }
+
+template <class F>
+static int fri_commit_layer_dev(int hash, const typename F::T* d_evals, uint64_t n, uint32_t ff, typename F::T* d_transposed,
+                                uint8_t* d_leaves, uint8_t* d_nodes, cudaStream_t stream) {
+  typedef typename F::T T;
+  if (!fri_folding_ok(ff)) return fail(WG_ERR_UNSUPPORTED, "folding factor %u is not supported", ff);  // prover/mod.rs:186
+  if (n == 0 || n % ff) return fail(WG_ERR_ARG, "source length must be divisible by %u, but was %llu", ff, (unsigned long long)n);
+  const uint64_t rows = n / ff;
+  if (rows < 2) return fail(WG_ERR_TOO_FEW, "a Merkle tree needs at least 2 leaves, got %llu", (unsigned long long)rows);
+  if (!is_pow2(rows)) return fail(WG_ERR_NOT_POW2, "number of leaves %llu is not a power of two", (unsigned long long)rows);
+  {
+    ProfScope ps(PH_HASH, stream);
+    fri_transpose_kernel<T><<<cdiv(n, 256), 256, 0, stream>>>(d_evals, d_transposed, rows, (uint32_t)ilog2(ff));
+    CUDA_TRY(cudaGetLastError());
+    g_launches++;
+  }
+  const void* ptrs[1] = {d_transposed};
+  const uint64_t rw = ff;
+  WG_TRY(hash_rows_dev<F>(hash, 1, ptrs, &rw, &rw, rows, d_leaves, stream));
+  return merkle_dev(hash, d_leaves, rows, d_nodes, stream);
+}
+
+template <class F>
+static int fri_apply_drp_dev(const typename F::T* d_transposed, uint64_t rows, uint32_t ff, typename F::T offset,
+                             typename F::T alpha, typename F::T* d_out, cudaStream_t stream) {
+  typedef typename F::T T;
+  if (!fri_folding_ok(ff)) return fail(WG_ERR_UNSUPPORTED, "folding factor %u is not supported", ff);
+  if (rows == 0) return WG_OK;
+  if (!is_pow2(rows)) return fail(WG_ERR_NOT_POW2, "number of rows %llu is not a power of two", (unsigned long long)rows);
+  const int log_n = ilog2(rows * ff);
+  if (log_n > F::kTwoAdicity || log_n > FRI_MAX_LOG_DOMAIN)
+    return fail(WG_ERR_TOO_LARGE, "multiplicative subgroup of size 2^%d does not exist in the specified base field", log_n);
+  if (F::is_zero(offset)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
+  if (!elem_is_canonical<F>(alpha) || !elem_is_canonical<F>(offset)) return fail(WG_ERR_ARG, "alpha / offset not a reduced field element");
+  FriFoldArgs<F> a;
+  memset(&a, 0, sizeof a);
+  a.rows_in = d_transposed;
+  a.out = d_out;
+  a.rows = rows;
+  a.log_rows = (uint32_t)ilog2(rows);
+  a.alpha_sinv0 = F::mul(alpha, f_inv<F>(offset));
+  a.n_inv = f_inv<F>(F::from_u64(ff));
+  T gi = f_inv<F>(f_root_of_unity<F>(log_n));
+  for (uint32_t b = 0; b < a.log_rows; b++) {
+    a.ginv_pow[b] = gi;
+    gi = F::mul(gi, gi);
+  }
+  ProfScope ps(PH_LDE_B, stream);
+  const unsigned blocks = cdiv(rows, 128);
+  switch (ff) {
+    case 2: fri_fold_kernel<F, 1><<<blocks, 128, 0, stream>>>(a); break;
+    case 4: fri_fold_kernel<F, 2><<<blocks, 128, 0, stream>>>(a); break;
+    case 8: fri_fold_kernel<F, 3><<<blocks, 128, 0, stream>>>(a); break;
+    default: fri_fold_kernel<F, 4><<<blocks, 128, 0, stream>>>(a); break;
+  }
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  return WG_OK;
+}
+
+template <class F>
+static int h_fri_commit_layer(int hash, const void* evals, uint64_t n, uint32_t ff, void* transposed_out, uint8_t* leaves_out,
+                              uint8_t* nodes_out) {
+  typedef typename F::T T;
+  if (!fri_folding_ok(ff)) return fail(WG_ERR_UNSUPPORTED, "folding factor %u is not supported", ff);
+  if (n == 0 || n % ff) return fail(WG_ERR_ARG, "source length must be divisible by %u, but was %llu", ff, (unsigned long long)n);
+  const uint64_t rows = n / ff;
+  DevBuf e, t, l, nd;
+  WG_TRY(e.alloc(n * sizeof(T)));
+  WG_TRY(t.alloc(n * sizeof(T)));
+  WG_TRY(l.alloc(rows * 32));
+  WG_TRY(nd.alloc(rows * 32));
+  CUDA_TRY(cudaMemcpyAsync(e.p, evals, n * sizeof(T), cudaMemcpyHostToDevice, 0));
+  WG_TRY(fri_commit_layer_dev<F>(hash, e.as<T>(), n, ff, t.as<T>(), l.as<uint8_t>(), nd.as<uint8_t>(), 0));
+  if (transposed_out) CUDA_TRY(cudaMemcpyAsync(transposed_out, t.p, n * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaMemcpyAsync(nodes_out, nd.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+template <class F>
+static int h_fri_apply_drp(const void* transposed, uint64_t rows, uint32_t ff, const void* offset, const void* alpha, void* out) {
+  typedef typename F::T T;
+  if (!fri_folding_ok(ff)) return fail(WG_ERR_UNSUPPORTED, "folding factor %u is not supported", ff);
+  DevBuf t, o;
+  WG_TRY(t.alloc(rows * ff * sizeof(T)));
+  WG_TRY(o.alloc(rows * sizeof(T)));
+  CUDA_TRY(cudaMemcpyAsync(t.p, transposed, rows * ff * sizeof(T), cudaMemcpyHostToDevice, 0));
+  WG_TRY(fri_apply_drp_dev<F>(t.as<T>(), rows, ff, offset_from_internal<F>(offset), offset_from_internal<F>(alpha), o.as<T>(), 0));
+  CUDA_TRY(cudaMemcpyAsync(out, o.p, rows * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
 }  // namespace wg
 
 // ================================================================================================ extern "C"
@@ -1456,6 +1563,43 @@ int wg_commit_trace_dev(int field, int hash, uint64_t n_rows, uint64_t blowup, u
   WG_FIELD_DISPATCH(field,
                     commit_trace_dev<Gl64>(hash, n_rows, blowup, n_traces, cols_per_trace, (const uint64_t*)d_cols, (uint64_t*)d_polys, d_ldes, (uint8_t*)d_leaves, (uint8_t*)d_nodes, (uint64_t*)d_scratch, scratch_elems, s),
                     commit_trace_dev<F128>(hash, n_rows, blowup, n_traces, cols_per_trace, (const u128*)d_cols, (u128*)d_polys, d_ldes, (uint8_t*)d_leaves, (uint8_t*)d_nodes, (u128*)d_scratch, scratch_elems, s));
+}
+
+// ---- FRI layers
+int wg_fri_commit_layer(int field, int hash, const void* evaluations, uint64_t n, uint32_t folding_factor, void* transposed_out,
+                        uint8_t* leaves_out, uint8_t* nodes_out) {
+  if (!evaluations || !nodes_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_fri_commit_layer<Gl64>(hash, evaluations, n, folding_factor, transposed_out, leaves_out, nodes_out),
+                    h_fri_commit_layer<F128>(hash, evaluations, n, folding_factor, transposed_out, leaves_out, nodes_out));
+}
+
+int wg_fri_apply_drp(int field, const void* transposed, uint64_t rows, uint32_t folding_factor, const void* domain_offset,
+                     const void* alpha, void* out) {
+  if (!transposed || !domain_offset || !alpha || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_fri_apply_drp<Gl64>(transposed, rows, folding_factor, domain_offset, alpha, out),
+                    h_fri_apply_drp<F128>(transposed, rows, folding_factor, domain_offset, alpha, out));
+}
+
+int wg_fri_commit_layer_dev(int field, int hash, const void* d_evaluations, uint64_t n, uint32_t folding_factor,
+                            void* d_transposed, void* d_leaves, void* d_nodes, void* stream) {
+  if (!d_evaluations || !d_transposed || !d_leaves || !d_nodes) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field,
+                    fri_commit_layer_dev<Gl64>(hash, (const uint64_t*)d_evaluations, n, folding_factor, (uint64_t*)d_transposed, (uint8_t*)d_leaves, (uint8_t*)d_nodes, s),
+                    fri_commit_layer_dev<F128>(hash, (const u128*)d_evaluations, n, folding_factor, (u128*)d_transposed, (uint8_t*)d_leaves, (uint8_t*)d_nodes, s));
+}
+
+int wg_fri_apply_drp_dev(int field, const void* d_transposed, uint64_t rows, uint32_t folding_factor, const void* domain_offset_host,
+                         const void* alpha_host, void* d_out, void* stream) {
+  if (!d_transposed || !domain_offset_host || !alpha_host || !d_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field,
+                    fri_apply_drp_dev<Gl64>((const uint64_t*)d_transposed, rows, folding_factor, offset_from_internal<Gl64>(domain_offset_host), offset_from_internal<Gl64>(alpha_host), (uint64_t*)d_out, s),
+                    fri_apply_drp_dev<F128>((const u128*)d_transposed, rows, folding_factor, offset_from_internal<F128>(domain_offset_host), offset_from_internal<F128>(alpha_host), (u128*)d_out, s));
 }
 
 }  // extern "C"
