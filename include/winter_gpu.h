@@ -151,6 +151,29 @@ int wg_fri_commit_layer(int field, int hash, const void* evaluations, uint64_t n
 int wg_fri_apply_drp(int field, const void* transposed, uint64_t rows, uint32_t folding_factor, const void* domain_offset,
                      const void* alpha, void* out);
 
+/* ---- extension-field element layouts ------------------------------------------------------------
+ * The fft:: functions are generic over E: FieldElement<BaseField = B> (math/src/fft/mod.rs:85,171,274,362) with BASE-field
+ * twiddles and offsets; callers with E != B are DEEP composition (prover/src/composer/mod.rs:199), the constraint evaluation
+ * table (prover/src/constraints/evaluation_table.rs:180-181,216), FRI remainders and the auxiliary trace segments
+ * (prover/src/lib.rs:333-334). An E element is ext_degree (1, 2 or 3) consecutive base elements in memory
+ * (math/src/field/extensions/quadratic.rs:28, cubic.rs:28); lengths n count E elements. Same conventions and error
+ * codes as the base-field functions above. In wg_evaluate_polys_over_ext / wg_commit_trace_ext a column holds n E
+ * elements, n_cols / cols_per_trace count E columns, and the row-major LDE has n_cols*ext_degree base elements per row
+ * (row width 8*ceil(n_cols*ext_degree/8)), exactly RowMatrix<E> (prover/src/matrix/row_matrix.rs:33-41). */
+int wg_interpolate_poly_ext(int field, uint32_t ext_degree, void* evals, uint64_t n, const void* inv_twiddles);
+int wg_interpolate_poly_with_offset_ext(int field, uint32_t ext_degree, void* evals, uint64_t n, const void* inv_twiddles,
+                                        const void* offset);
+int wg_evaluate_poly_ext(int field, uint32_t ext_degree, void* p, uint64_t n, const void* twiddles);
+int wg_evaluate_poly_with_offset_ext(int field, uint32_t ext_degree, const void* p, uint64_t n, const void* twiddles,
+                                     const void* offset, uint64_t blowup, void* out);
+int wg_interpolate_columns_ext(int field, uint32_t ext_degree, const void* const* columns, uint32_t n_cols, uint64_t n,
+                               void* const* polys_out);
+int wg_evaluate_polys_over_ext(int field, uint32_t ext_degree, const void* const* polys, uint32_t n_cols, uint64_t n,
+                               uint64_t blowup, const void* offset, void* out);
+int wg_commit_trace_ext(int field, int hash, uint32_t ext_degree, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                        const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
+                        void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out);
+
 /* ---- device-resident entry points (no host transfers; what bench.py's `value` times) -------------------- */
 /* All pointers are device pointers on the wg_init device; `stream` is a cudaStream_t (NULL = default stream).
  * Column matrices are contiguous: element (c, r) at [c*n + r]. */

@@ -191,3 +191,41 @@ def fri_apply_drp(field, transposed, folding, offset, alpha):
     if rc:
         raise ValueError(f"or_fri_apply_drp rc={rc}")
     return out
+
+
+def interpolate_poly_ext(field, deg, evals, offset=None):
+    """fft::interpolate_poly / interpolate_poly_with_offset for E = degree-`deg` extension; evals [n, deg(,2)]."""
+    v = np.ascontiguousarray(evals, dtype=np.uint64).copy()
+    n = v.shape[0]
+    inv_tw = np.ascontiguousarray(get_twiddles(field, n, True))
+    off = np.ascontiguousarray(offset, dtype=np.uint64) if offset is not None else None
+    rc = lib().or_interpolate_poly_ext(field, C.c_uint32(deg), _p(v), C.c_uint64(n), _p(inv_tw), _p(off))
+    if rc:
+        raise ValueError(f"or_interpolate_poly_ext rc={rc}")
+    return v
+
+
+def evaluate_poly_with_offset_ext(field, deg, p, offset, blowup):
+    p = np.ascontiguousarray(p, dtype=np.uint64)
+    n = p.shape[0]
+    tw = np.ascontiguousarray(get_twiddles(field, n))
+    out = np.empty((n * blowup,) + p.shape[1:], dtype=np.uint64)
+    rc = lib().or_evaluate_poly_with_offset_ext(field, C.c_uint32(deg), _p(p), C.c_uint64(n), _p(tw),
+                                                _p(np.ascontiguousarray(offset, dtype=np.uint64)), C.c_uint64(blowup), _p(out))
+    if rc:
+        raise ValueError(f"or_evaluate_poly_with_offset_ext rc={rc}")
+    return out
+
+
+def split_ext_columns(field, cols):
+    """[C, n, deg(,2)] extension columns -> [C*deg, n(,2)] base columns, base column c*deg + d = coordinate d of column c
+    (ColMatrix::get_base_element, prover/src/matrix/col_matrix.rs:113-119)."""
+    a = np.asarray(cols, dtype=np.uint64)
+    a = np.moveaxis(a, 2, 1)  # [C, deg, n(,2)]
+    return np.ascontiguousarray(a.reshape((a.shape[0] * a.shape[1],) + a.shape[2:]))
+
+
+def merge_ext_columns(field, base_cols, deg):
+    a = np.asarray(base_cols, dtype=np.uint64)
+    a = a.reshape((a.shape[0] // deg, deg) + a.shape[1:])
+    return np.ascontiguousarray(np.moveaxis(a, 1, 2))

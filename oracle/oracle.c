@@ -27,8 +27,10 @@
 #define FADD f64_add
 #define FSUB f64_sub
 #define FMUL f64_mul
+#define FEXP f64_exp
 #define NAME(x) f64_##x
 #include "oracle_ntt_impl.h"
+#undef FEXP
 #undef FE
 #undef FADD
 #undef FSUB
@@ -39,8 +41,10 @@
 #define FADD f128_add
 #define FSUB f128_sub
 #define FMUL f128_mul
+#define FEXP f128_exp
 #define NAME(x) f128_##x
 #include "oracle_ntt_impl.h"
+#undef FEXP
 #undef FE
 #undef FADD
 #undef FSUB
@@ -483,6 +487,54 @@ int or_fri_apply_drp(int field, const void* transposed, uint64_t rows, uint32_t 
       res[i] = acc;
       s = f128_mul(s, g_inv);
     }
+  }
+  return OR_OK;
+}
+
+
+/* ================================================================================================ extension fields
+ * (SURVEY 8(f) rank 4). QuadExtension<B> / CubeExtension<B> elements are 2 / 3 consecutive base elements
+ * (math/src/field/extensions/quadratic.rs:28, cubic.rs:28) and the FFT functions multiply them by BASE-field twiddles and
+ * offsets only (`FftInputs for [E]`, math/src/fft/fft_inputs.rs:101-144: `mul_base`), which acts on every coordinate
+ * separately. The generic NTT above already works on rows of w elements, so E = degree-w extension is the w-wide case. */
+int or_interpolate_poly_ext(int field, uint32_t deg, void* evals, uint64_t n, const void* inv_tw, const void* offset) {
+  if (!is_pow2(n)) return OR_ERR_NOT_POW2;
+  if (ilog2(n) > (field == 0 ? F64_TWO_ADICITY : F128_TWO_ADICITY)) return OR_ERR_TOO_LARGE;
+  if (field == 0) {
+    uint64_t off_inv = f64_new(1);
+    if (offset) {
+      if (*(const uint64_t*)offset == 0) return OR_ERR_ZERO_OFFSET;
+      off_inv = f64_inv(*(const uint64_t*)offset);
+    }
+    f64_interpolate_w((uint64_t*)evals, n, deg, (const uint64_t*)inv_tw, f64_inv(f64_new(n)), off_inv);
+  } else {
+    u128 off_inv = 1;
+    if (offset) {
+      u128 o;
+      memcpy(&o, offset, 16);
+      if (o == 0) return OR_ERR_ZERO_OFFSET;
+      off_inv = f128_inv(o);
+    }
+    f128_interpolate_w((u128*)evals, n, deg, (const u128*)inv_tw, f128_inv((u128)n), off_inv);
+  }
+  return OR_OK;
+}
+
+int or_evaluate_poly_with_offset_ext(int field, uint32_t deg, const void* p, uint64_t n, const void* tw, const void* offset,
+                                     uint64_t blowup, void* out) {
+  if (!is_pow2(n) || !is_pow2(blowup)) return OR_ERR_NOT_POW2;
+  uint64_t dom = n * blowup;
+  if (ilog2(dom) > (field == 0 ? F64_TWO_ADICITY : F128_TWO_ADICITY)) return OR_ERR_TOO_LARGE;
+  if (field == 0) {
+    uint64_t off = *(const uint64_t*)offset;
+    if (off == 0) return OR_ERR_ZERO_OFFSET;
+    f64_evaluate_offset_w((const uint64_t*)p, n, deg, (const uint64_t*)tw, f64_root_of_unity(ilog2(dom)), off, f64_new(1), blowup,
+                          (uint64_t*)out);
+  } else {
+    u128 off;
+    memcpy(&off, offset, 16);
+    if (off == 0) return OR_ERR_ZERO_OFFSET;
+    f128_evaluate_offset_w((const u128*)p, n, deg, (const u128*)tw, f128_root_of_unity(ilog2(dom)), off, 1, blowup, (u128*)out);
   }
   return OR_OK;
 }

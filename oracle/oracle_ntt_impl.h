@@ -78,3 +78,33 @@ static void NAME(power_series)(FE b, size_t n, FE one, FE* out) {
     acc = FMUL(acc, b);
   }
 }
+
+/* math/src/fft/serial.rs:64-73 (interpolate_poly) and :78-93 (interpolate_poly_with_offset) on rows of w coordinates:
+ * fft_in_place(inv_twiddles); coefficient k *= inv_len * offset_inv^k (offset_inv = 1 for the plain variant); permute.
+ * The reference scales before permuting (shift_by / the offset loop run on the bit-reversed vector in the plain
+ * variant and after permute in the offset variant); products commute, so one order is restated. */
+static void NAME(interpolate_w)(FE* v, size_t n, size_t w, const FE* inv_tw, FE inv_len, FE off_inv) {
+  NAME(fft_in_place)(v, n, w, inv_tw);
+  NAME(permute)(v, n, w);
+  FE f = inv_len;
+  for (size_t k = 0; k < n; k++) {
+    for (size_t t = 0; t < w; t++) v[k * w + t] = FMUL(v[k * w + t], f);
+    f = FMUL(f, off_inv);
+  }
+}
+
+/* math/src/fft/serial.rs:26-57 (evaluate_poly_with_offset) on rows of w coordinates: per coset i (bit-reversed order)
+ * scale coefficient k by (g^rev(i) * offset)^k, transform, then one global permute */
+static void NAME(evaluate_offset_w)(const FE* p, size_t n, size_t w, const FE* tw, FE g, FE off, FE one, size_t blowup, FE* out) {
+  for (size_t i = 0; i < blowup; i++) {
+    size_t idx = NAME(permute_index)(blowup, i);
+    FE o = FMUL(FEXP(g, idx), off), factor = one;
+    FE* chunk = out + i * n * w;
+    for (size_t k = 0; k < n; k++) {
+      for (size_t t = 0; t < w; t++) chunk[k * w + t] = FMUL(p[k * w + t], factor);
+      factor = FMUL(factor, o);
+    }
+    NAME(fft_in_place)(chunk, n, w, tw);
+  }
+  NAME(permute)(out, n * blowup, w);
+}

@@ -23,6 +23,8 @@ SYMBOLS = [
     "wg_commit_polys", "wg_commitment_from_trace", "wg_commitment_from_polys", "wg_commitment_info", "wg_commitment_rows",
     "wg_commitment_digests", "wg_commitment_download", "wg_commitment_free",
     "wg_fri_commit_layer", "wg_fri_apply_drp", "wg_fri_commit_layer_dev", "wg_fri_apply_drp_dev",
+    "wg_interpolate_poly_ext", "wg_interpolate_poly_with_offset_ext", "wg_evaluate_poly_ext", "wg_evaluate_poly_with_offset_ext",
+    "wg_interpolate_columns_ext", "wg_evaluate_polys_over_ext", "wg_commit_trace_ext",
 ]
 
 
@@ -84,6 +86,13 @@ def lib():
         L.wg_fri_apply_drp.argtypes = [i32, vp, u64, u32, vp, vp, vp]
         L.wg_fri_commit_layer_dev.argtypes = [i32, i32, vp, u64, u32, vp, vp, vp, vp]
         L.wg_fri_apply_drp_dev.argtypes = [i32, vp, u64, u32, vp, vp, vp, vp]
+        L.wg_interpolate_poly_ext.argtypes = [i32, u32, vp, u64, vp]
+        L.wg_interpolate_poly_with_offset_ext.argtypes = [i32, u32, vp, u64, vp, vp]
+        L.wg_evaluate_poly_ext.argtypes = [i32, u32, vp, u64, vp]
+        L.wg_evaluate_poly_with_offset_ext.argtypes = [i32, u32, vp, u64, vp, vp, u64, vp]
+        L.wg_interpolate_columns_ext.argtypes = [i32, u32, vp, u32, u64, vp]
+        L.wg_evaluate_polys_over_ext.argtypes = [i32, u32, vp, u32, u64, u64, vp, vp]
+        L.wg_commit_trace_ext.argtypes = [i32, i32, u32, u64, u64, u32, vp, vp, vp, vp, vp, vp, vp]
         _lib = L
     return _lib
 

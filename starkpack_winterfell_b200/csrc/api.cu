@@ -747,22 +747,78 @@ static int h_get_twiddles(uint64_t n, int inverse, void* out) {
   return WG_OK;
 }
 
+// Extension-field element layouts: a QuadExtension / CubeExtension element is `deg` consecutive base
+// elements (math/src/field/extensions/quadratic.rs:28, cubic.rs:28) and every fft:: function multiplies it by base-field
+// twiddles only (fft_inputs.rs:101-144 `mul_base`), i.e. acts per coordinate. A column of E elements [n][deg] is therefore
+// split into deg base columns on the device, transformed by the base-field kernels, and merged back.
+template <class T>
+__global__ void __launch_bounds__(256) deinterleave_kernel(const T* __restrict__ in, T* __restrict__ out, uint64_t n, uint32_t deg) {
+  const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;  // out [deg][n]
+  if (idx >= n * deg) return;
+  const uint64_t d = idx / n, i = idx - d * n;
+  out[idx] = in[i * deg + d];
+}
+template <class T>
+__global__ void __launch_bounds__(256) interleave_kernel(const T* __restrict__ in, T* __restrict__ out, uint64_t n, uint32_t deg) {
+  const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;  // out [n][deg]
+  if (idx >= n * deg) return;
+  const uint64_t i = idx / deg, d = idx - i * deg;
+  out[idx] = in[d * n + i];
+}
+static inline int check_ext_degree(uint32_t deg) {
+  if (deg < 1 || deg > 3) return fail(WG_ERR_UNSUPPORTED, "extension degree %u is not supported (1, 2, 3)", deg);
+  return WG_OK;
+}
+
+// Uploads n_cols host columns of n extension elements each and leaves them on the device as n_cols*deg base columns
+// [c*deg + d][n] in `dst` (deg = 1: a plain copy per column). `stg` is scratch of the same size.
+template <class T>
+static int upload_columns(const void* const* cols, uint32_t n_cols, uint64_t n, uint32_t deg, T* dst, T* stg, cudaStream_t s) {
+  const size_t colb = n * deg * sizeof(T);
+  char* to = reinterpret_cast<char*>(deg == 1 ? dst : stg);
+  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(to + c * colb, cols[c], colb, cudaMemcpyHostToDevice, s));
+  if (deg > 1) {
+    for (uint32_t c = 0; c < n_cols; c++) {
+      deinterleave_kernel<T><<<cdiv(n * deg, 256), 256, 0, s>>>(stg + (size_t)c * n * deg, dst + (size_t)c * n * deg, n, deg);
+      CUDA_TRY(cudaGetLastError());
+      g_launches++;
+    }
+  }
+  return WG_OK;
+}
+template <class T>
+static int download_columns(void* const* outs, uint32_t n_cols, uint64_t n, uint32_t deg, const T* src, T* stg, cudaStream_t s) {
+  const size_t colb = n * deg * sizeof(T);
+  if (deg > 1) {
+    for (uint32_t c = 0; c < n_cols; c++) {
+      interleave_kernel<T><<<cdiv(n * deg, 256), 256, 0, s>>>(src + (size_t)c * n * deg, stg + (size_t)c * n * deg, n, deg);
+      CUDA_TRY(cudaGetLastError());
+      g_launches++;
+    }
+  }
+  const char* from = reinterpret_cast<const char*>(deg == 1 ? src : stg);
+  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(outs[c], from + c * colb, colb, cudaMemcpyDeviceToHost, s));
+  return WG_OK;
+}
+
 template <class F>
-static int h_interpolate_columns(const void* const* cols, uint32_t n_cols, uint64_t n, void* const* outs) {
+static int h_interpolate_columns(const void* const* cols, uint32_t n_cols, uint64_t n, void* const* outs, uint32_t deg = 1) {
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, 1));
+  WG_TRY(check_ext_degree(deg));
   DevBuf in, out, scr;
+  const uint32_t nb = n_cols * deg;  // base columns
   const size_t colb = n * sizeof(T);
-  WG_TRY(in.alloc(colb * n_cols));
-  WG_TRY(out.alloc(colb * n_cols));
-  const uint64_t se = interpolate_scratch_elems<F>(n_cols, n);
+  WG_TRY(in.alloc(colb * nb));
+  WG_TRY(out.alloc(colb * nb));
+  const uint64_t se = interpolate_scratch_elems<F>(nb, n);
   WG_TRY(scr.alloc(se * sizeof(T)));
-  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(in.as<char>() + c * colb, cols[c], colb, cudaMemcpyHostToDevice, 0));
-  for (uint32_t c0 = 0; c0 < n_cols; c0 += 65535) {
-    uint32_t nc = (n_cols - c0) < 65535 ? (n_cols - c0) : 65535;
+  WG_TRY(upload_columns<T>(cols, n_cols, n, deg, in.as<T>(), out.as<T>(), 0));
+  for (uint32_t c0 = 0; c0 < nb; c0 += 65535) {
+    uint32_t nc = (nb - c0) < 65535 ? (nb - c0) : 65535;
     WG_TRY(interpolate_columns_dev<F>(in.as<T>() + (size_t)c0 * n, nc, n, out.as<T>() + (size_t)c0 * n, scr.as<T>(), se, 0));
   }
-  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(outs[c], out.as<char>() + c * colb, colb, cudaMemcpyDeviceToHost, 0));
+  WG_TRY(download_columns<T>(outs, n_cols, n, deg, out.as<T>(), in.as<T>(), 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -777,42 +833,50 @@ __global__ void scale_powers_kernel(typename F::T* x, uint64_t n, const typename
 // fft::interpolate_poly_with_offset (math/src/fft/mod.rs:362-400; serial.rs:78-93): inverse transform, then
 // coefficient i times offset^-i
 template <class F>
-static int h_interpolate_poly_with_offset(void* evals, uint64_t n, const void* offset) {
+static int h_interpolate_poly_with_offset(void* evals, uint64_t n, const void* offset, uint32_t deg = 1) {
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, 1));
+  WG_TRY(check_ext_degree(deg));
   const T off = offset_from_internal<F>(offset);
   if (F::is_zero(off)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
   DevBuf in, out, scr;
-  WG_TRY(in.alloc(n * sizeof(T)));
-  WG_TRY(out.alloc(n * sizeof(T)));
-  const uint64_t se = interpolate_scratch_elems<F>(1, n);
+  WG_TRY(in.alloc(n * deg * sizeof(T)));
+  WG_TRY(out.alloc(n * deg * sizeof(T)));
+  const uint64_t se = interpolate_scratch_elems<F>(deg, n);
   WG_TRY(scr.alloc(se * sizeof(T)));
-  CUDA_TRY(cudaMemcpyAsync(in.p, evals, n * sizeof(T), cudaMemcpyHostToDevice, 0));
-  WG_TRY(interpolate_columns_dev<F>(in.as<T>(), 1, n, out.as<T>(), scr.as<T>(), se, 0));
+  const void* cols[1] = {evals};
+  void* outs[1] = {evals};
+  WG_TRY(upload_columns<T>(cols, 1, n, deg, in.as<T>(), out.as<T>(), 0));
+  WG_TRY(interpolate_columns_dev<F>(in.as<T>(), deg, n, out.as<T>(), scr.as<T>(), se, 0));
   typename Tables<F>::Two pm;
   long long zl, zh;
   WG_TRY(tables<F>().get_pm(ilog2(n), 0, f_inv<F>(off), &pm, &zl, &zh));
-  scale_powers_kernel<F><<<cdiv(n, 256), 256, 0, 0>>>(out.as<T>(), n, pm.lo, pm.hi, (uint32_t)pm.lb);
-  CUDA_TRY(cudaGetLastError());
-  g_launches++;
-  CUDA_TRY(cudaMemcpyAsync(evals, out.p, n * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  for (uint32_t d = 0; d < deg; d++) {
+    scale_powers_kernel<F><<<cdiv(n, 256), 256, 0, 0>>>(out.as<T>() + (size_t)d * n, n, pm.lo, pm.hi, (uint32_t)pm.lb);
+    CUDA_TRY(cudaGetLastError());
+    g_launches++;
+  }
+  WG_TRY(download_columns<T>(outs, 1, n, deg, out.as<T>(), in.as<T>(), 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
 
 template <class F>
 static int h_evaluate_polys_over(const void* const* polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset,
-                                 void* out, uint64_t row_width) {
+                                 void* out, uint64_t row_width, uint32_t deg = 1) {
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, blowup));
-  DevBuf in, lde, scr;
+  WG_TRY(check_ext_degree(deg));
+  DevBuf in, stg, lde, scr;
+  const uint32_t nb = n_cols * deg;
   const size_t colb = n * sizeof(T);
-  WG_TRY(in.alloc(colb * n_cols));
+  WG_TRY(in.alloc(colb * nb));
+  if (deg > 1) WG_TRY(stg.alloc(colb * nb));
   WG_TRY(lde.alloc(n * blowup * row_width * sizeof(T)));
-  const uint64_t se = lde_scratch_elems<F>(n_cols, n, blowup);
+  const uint64_t se = lde_scratch_elems<F>(nb, n, blowup);
   WG_TRY(scr.alloc(se * sizeof(T)));
-  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(in.as<char>() + c * colb, polys[c], colb, cudaMemcpyHostToDevice, 0));
-  WG_TRY(lde_dev<F>(in.as<T>(), n_cols, n, blowup, offset_from_internal<F>(offset), lde.as<T>(), row_width, scr.as<T>(), se, 0));
+  WG_TRY(upload_columns<T>(polys, n_cols, n, deg, in.as<T>(), stg.as<T>(), 0));
+  WG_TRY(lde_dev<F>(in.as<T>(), nb, n, blowup, offset_from_internal<F>(offset), lde.as<T>(), row_width, scr.as<T>(), se, 0));
   CUDA_TRY(cudaMemcpyAsync(out, lde.p, n * blowup * row_width * sizeof(T), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
@@ -958,6 +1022,62 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   CUDA_TRY(cudaStreamSynchronize(sx));
   CUDA_TRY(cudaStreamSynchronize(sc));
   CUDA_TRY(cudaStreamSynchronize(sh));
+  return WG_OK;
+}
+
+// Prover::build_trace_commitment::<E> for an extension field E (auxiliary trace segments, prover/src/lib.rs:333-334):
+// the same path on n_cols*deg base columns (ColMatrix::get_base_element, col_matrix.rs:113-119; RowMatrix keeps base
+// elements, row_matrix.rs:33-41). Not pipelined like h_commit_trace: auxiliary segments are a few columns.
+template <class F>
+static int h_commit_trace_ext(int hash, uint32_t deg, uint64_t n, uint64_t blowup, uint32_t n_traces, const uint32_t* cols_per_trace,
+                              const void* const* column_ptrs, void* const* polys_out, void* const* lde_out, uint8_t* leaves_out,
+                              uint8_t* nodes_out, uint8_t* root_out) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, blowup));
+  WG_TRY(check_ext_degree(deg));
+  if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
+  uint64_t total = 0, max_cols = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    if (cols_per_trace[t] == 0) return fail(WG_ERR_ARG, "trace %u has no columns", t);
+    total += cols_per_trace[t];
+    if (cols_per_trace[t] > max_cols) max_cols = cols_per_trace[t];
+  }
+  if (total * deg > 65535) return fail(WG_ERR_UNSUPPORTED, "too many columns");
+  const uint32_t nb = (uint32_t)(total * deg);
+  const uint64_t L = n * blowup;
+  DevBuf cols, polys, scr, leaves, nodes;
+  WG_TRY(cols.alloc((size_t)nb * n * sizeof(T)));
+  WG_TRY(polys.alloc((size_t)nb * n * sizeof(T)));
+  uint64_t se = interpolate_scratch_elems<F>(nb, n);
+  const uint64_t se2 = lde_scratch_elems<F>((uint32_t)(max_cols * deg), n, blowup);
+  if (se2 > se) se = se2;
+  WG_TRY(scr.alloc(se * sizeof(T)));
+  WG_TRY(leaves.alloc(L * 32));
+  WG_TRY(nodes.alloc(L * 32));
+  std::vector<DevBuf> ldes(n_traces);
+  std::vector<uint64_t> rws(n_traces), els(n_traces);
+  std::vector<const void*> lde_c(n_traces);
+  for (uint32_t t = 0; t < n_traces; t++) {
+    els[t] = (uint64_t)cols_per_trace[t] * deg;
+    rws[t] = (els[t] + 7) / 8 * 8;
+    WG_TRY(ldes[t].alloc(L * rws[t] * sizeof(T)));
+    lde_c[t] = ldes[t].p;
+  }
+  WG_TRY(upload_columns<T>(column_ptrs, (uint32_t)total, n, deg, cols.as<T>(), polys.as<T>(), 0));
+  WG_TRY(interpolate_columns_dev<F>(cols.as<T>(), nb, n, polys.as<T>(), scr.as<T>(), se, 0));
+  uint64_t c0 = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    WG_TRY(lde_dev<F>(polys.as<T>() + c0 * n, (uint32_t)els[t], n, blowup, generator<F>(), ldes[t].as<T>(), rws[t], scr.as<T>(), se, 0));
+    c0 += els[t];
+    if (lde_out && lde_out[t]) CUDA_TRY(cudaMemcpyAsync(lde_out[t], ldes[t].p, L * rws[t] * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  }
+  WG_TRY(hash_rows_dev<F>(hash, n_traces, lde_c.data(), rws.data(), els.data(), L, leaves.as<uint8_t>(), 0));
+  WG_TRY(merkle_dev(hash, leaves.as<uint8_t>(), L, nodes.as<uint8_t>(), 0));
+  if (polys_out) WG_TRY(download_columns<T>(polys_out, (uint32_t)total, n, deg, polys.as<T>(), cols.as<T>(), 0));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes.as<uint8_t>() + 32, 32, cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves.p, L * 32, cudaMemcpyDeviceToHost, 0));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes.p, L * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
 
@@ -1600,6 +1720,78 @@ int wg_fri_apply_drp_dev(int field, const void* d_transposed, uint64_t rows, uin
   WG_FIELD_DISPATCH(field,
                     fri_apply_drp_dev<Gl64>((const uint64_t*)d_transposed, rows, folding_factor, offset_from_internal<Gl64>(domain_offset_host), offset_from_internal<Gl64>(alpha_host), (uint64_t*)d_out, s),
                     fri_apply_drp_dev<F128>((const u128*)d_transposed, rows, folding_factor, offset_from_internal<F128>(domain_offset_host), offset_from_internal<F128>(alpha_host), (u128*)d_out, s));
+}
+
+// ---- extension-field element layouts
+int wg_interpolate_poly_ext(int field, uint32_t ext_degree, void* evals, uint64_t n, const void* inv_twiddles) {
+  (void)inv_twiddles;
+  if (!evals) return fail(WG_ERR_ARG, "null input");
+  WG_TRY(ensure_device());
+  const void* in[1] = {evals};
+  void* out[1] = {evals};
+  WG_FIELD_DISPATCH(field, h_interpolate_columns<Gl64>(in, 1, n, out, ext_degree), h_interpolate_columns<F128>(in, 1, n, out, ext_degree));
+}
+
+int wg_interpolate_poly_with_offset_ext(int field, uint32_t ext_degree, void* evals, uint64_t n, const void* inv_twiddles,
+                                        const void* offset) {
+  (void)inv_twiddles;
+  if (!evals || !offset) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_interpolate_poly_with_offset<Gl64>(evals, n, offset, ext_degree),
+                    h_interpolate_poly_with_offset<F128>(evals, n, offset, ext_degree));
+}
+
+int wg_evaluate_poly_ext(int field, uint32_t ext_degree, void* p, uint64_t n, const void* twiddles) {
+  (void)twiddles;
+  if (!p) return fail(WG_ERR_ARG, "null input");
+  WG_TRY(ensure_device());
+  const void* in[1] = {p};
+  if (field == WG_FIELD_F64) {
+    const Gl64::T one = Gl64::one();
+    return h_evaluate_polys_over<Gl64>(in, 1, n, 1, &one, p, ext_degree, ext_degree);
+  } else if (field == WG_FIELD_F128) {
+    const F128::T one = F128::one();
+    return h_evaluate_polys_over<F128>(in, 1, n, 1, &one, p, ext_degree, ext_degree);
+  }
+  return fail(WG_ERR_ARG, "unknown field %d", field);
+}
+
+int wg_evaluate_poly_with_offset_ext(int field, uint32_t ext_degree, const void* p, uint64_t n, const void* twiddles,
+                                     const void* offset, uint64_t blowup, void* out) {
+  (void)twiddles;
+  if (!p || !offset || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  const void* in[1] = {p};
+  WG_FIELD_DISPATCH(field, h_evaluate_polys_over<Gl64>(in, 1, n, blowup, offset, out, ext_degree, ext_degree),
+                    h_evaluate_polys_over<F128>(in, 1, n, blowup, offset, out, ext_degree, ext_degree));
+}
+
+int wg_interpolate_columns_ext(int field, uint32_t ext_degree, const void* const* columns, uint32_t n_cols, uint64_t n,
+                               void* const* polys_out) {
+  if (!columns || !polys_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_interpolate_columns<Gl64>(columns, n_cols, n, polys_out, ext_degree),
+                    h_interpolate_columns<F128>(columns, n_cols, n, polys_out, ext_degree));
+}
+
+int wg_evaluate_polys_over_ext(int field, uint32_t ext_degree, const void* const* polys, uint32_t n_cols, uint64_t n,
+                               uint64_t blowup, const void* offset, void* out) {
+  if (!polys || !offset || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_TRY(check_ext_degree(ext_degree));
+  const uint64_t rw = ((uint64_t)n_cols * ext_degree + 7) / 8 * 8;
+  WG_FIELD_DISPATCH(field, h_evaluate_polys_over<Gl64>(polys, n_cols, n, blowup, offset, out, rw, ext_degree),
+                    h_evaluate_polys_over<F128>(polys, n_cols, n, blowup, offset, out, rw, ext_degree));
+}
+
+int wg_commit_trace_ext(int field, int hash, uint32_t ext_degree, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
+                        const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
+                        void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out) {
+  if (!cols_per_trace || !column_ptrs) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field,
+                    h_commit_trace_ext<Gl64>(hash, ext_degree, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out, leaves_out, nodes_out, root_out),
+                    h_commit_trace_ext<F128>(hash, ext_degree, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out, leaves_out, nodes_out, root_out));
 }
 
 }  // extern "C"

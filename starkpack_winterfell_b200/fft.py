@@ -1,5 +1,9 @@
 """Mirror of winter_math::fft (math/src/fft/mod.rs) over the C ABI. Arrays are numpy uint64: f64 -> shape [n]
-(Montgomery words, the reference's internal representation), f128 -> shape [n, 2] (lo, hi)."""
+(Montgomery words, the reference's internal representation), f128 -> shape [n, 2] (lo, hi).
+
+The reference's functions are generic over E: FieldElement<BaseField = B>; `ext_degree` (1, 2, 3) selects E = B,
+QuadExtension<B>, CubeExtension<B>: an element is ext_degree consecutive base elements, arrays get one more axis
+(f64 [n, deg], f128 [n, deg, 2]); twiddles and offsets stay base-field elements."""
 import ctypes as C
 
 import numpy as np
@@ -37,7 +41,7 @@ def get_inv_twiddles(field, domain_size):
     return out[: domain_size // 2]
 
 
-def interpolate_poly(field, evaluations, inv_twiddles=None):
+def interpolate_poly(field, evaluations, inv_twiddles=None, ext_degree=1):
     """fft::interpolate_poly (math/src/fft/mod.rs:274-305): IN PLACE on `evaluations` (must be a contiguous
     uint64 numpy array). Same preconditions as the reference: power-of-two length, twiddles of length n/2."""
     v = evaluations
@@ -46,17 +50,23 @@ def interpolate_poly(field, evaluations, inv_twiddles=None):
     n = v.shape[0]
     if inv_twiddles is not None and len(inv_twiddles) * 2 != n:
         raise ValueError(f"invalid number of twiddles: expected {n // 2} but received {len(inv_twiddles)}")
+    if ext_degree != 1:
+        return check(lib().wg_interpolate_poly_ext(field, ext_degree, _p(v), n, None))
     check(lib().wg_interpolate_poly(field, _p(v), n, None))
 
 
-def evaluate_poly_with_offset(field, p, twiddles, domain_offset, blowup_factor):
+def evaluate_poly_with_offset(field, p, twiddles, domain_offset, blowup_factor, ext_degree=1):
     """fft::evaluate_poly_with_offset (math/src/fft/mod.rs:171-220). domain_offset is one element in internal
     representation (uint64 for f64 = Montgomery word; [lo, hi] for f128)."""
-    p = _n(field, p)
+    p = _n(field, p) if ext_degree == 1 else np.ascontiguousarray(p, dtype=np.uint64)
     n = p.shape[0]
     if twiddles is not None and len(twiddles) * 2 != n:
         raise ValueError(f"invalid number of twiddles: expected {n // 2} but received {len(twiddles)}")
     off = np.ascontiguousarray(domain_offset, dtype=np.uint64).reshape(-1)
+    if ext_degree != 1:
+        out = np.empty((n * blowup_factor,) + p.shape[1:], dtype=np.uint64)
+        check(lib().wg_evaluate_poly_with_offset_ext(field, ext_degree, _p(p), n, None, _p(off), blowup_factor, _p(out)))
+        return out
     out = _elems(field, n * blowup_factor)
     check(lib().wg_evaluate_poly_with_offset(field, _p(p), n, None, _p(off), blowup_factor, _p(out)))
     return out
@@ -68,26 +78,30 @@ def _inplace(v, what):
     return v.shape[0]
 
 
-def evaluate_poly(field, p, twiddles=None):
+def evaluate_poly(field, p, twiddles=None, ext_degree=1):
     """fft::evaluate_poly (math/src/fft/mod.rs:85-116): IN PLACE, p[k] <- P(w_n^k), natural order."""
     n = _inplace(p, "p")
     if twiddles is not None and len(twiddles) * 2 != n:
         raise ValueError(f"invalid number of twiddles: expected {n // 2} but received {len(twiddles)}")
+    if ext_degree != 1:
+        return check(lib().wg_evaluate_poly_ext(field, ext_degree, _p(p), n, None))
     check(lib().wg_evaluate_poly(field, _p(p), n, None))
 
 
-def serial_fft(field, values, twiddles=None):
+def serial_fft(field, values, twiddles=None, ext_degree=1):
     """fft::serial_fft (math/src/fft/mod.rs:416-440): fft_in_place followed by permute, i.e. the natural-order transform."""
-    evaluate_poly(field, values, twiddles)
+    evaluate_poly(field, values, twiddles, ext_degree)
 
 
-def interpolate_poly_with_offset(field, evaluations, inv_twiddles, domain_offset):
+def interpolate_poly_with_offset(field, evaluations, inv_twiddles, domain_offset, ext_degree=1):
     """fft::interpolate_poly_with_offset (math/src/fft/mod.rs:362-400): IN PLACE; evaluations were taken over the coset
     domain_offset * <w_n>. domain_offset is one element in internal representation."""
     n = _inplace(evaluations, "evaluations")
     if inv_twiddles is not None and len(inv_twiddles) * 2 != n:
         raise ValueError(f"invalid number of twiddles: expected {n // 2} but received {len(inv_twiddles)}")
     off = np.ascontiguousarray(domain_offset, dtype=np.uint64).reshape(-1)
+    if ext_degree != 1:
+        return check(lib().wg_interpolate_poly_with_offset_ext(field, ext_degree, _p(evaluations), n, None, _p(off)))
     check(lib().wg_interpolate_poly_with_offset(field, _p(evaluations), n, None, _p(off)))
 
 

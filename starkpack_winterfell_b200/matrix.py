@@ -47,8 +47,10 @@ class StarkDomain:
 class ColMatrix:
     """prover/src/matrix/col_matrix.rs:31-69: a list of separately allocated columns."""
 
-    def __init__(self, field, columns):
+    def __init__(self, field, columns, ext_degree=1):
+        """ext_degree > 1: ColMatrix<E> over a quadratic / cubic extension; a column is [n, deg] (f64) or [n, deg, 2]."""
         self.field = field
+        self.ext_degree = ext_degree
         self.columns = [np.ascontiguousarray(c, dtype=np.uint64) for c in columns]
         assert len(self.columns) > 0, "a matrix must contain at least one column"
         n = self.columns[0].shape[0]
@@ -61,9 +63,17 @@ class ColMatrix:
     def num_rows(self):
         return self.columns[0].shape[0]
 
+    def num_base_cols(self):
+        """col_matrix.rs:78-80"""
+        return len(self.columns) * self.ext_degree
+
     def interpolate_columns(self):
         """ColMatrix::interpolate_columns (col_matrix.rs:196-206): new matrix, input untouched."""
         outs = [np.empty_like(c) for c in self.columns]
+        if self.ext_degree != 1:
+            check(lib().wg_interpolate_columns_ext(self.field, self.ext_degree, _ptr_array(self.columns), len(outs), self.num_rows(),
+                                                   _ptr_array(outs)))
+            return ColMatrix(self.field, outs, self.ext_degree)
         check(lib().wg_interpolate_columns(self.field, _ptr_array(self.columns), len(outs), self.num_rows(), _ptr_array(outs)))
         return ColMatrix(self.field, outs)
 
@@ -78,6 +88,14 @@ class RowMatrix:
     def evaluate_polys_over(cls, polys, domain):
         """RowMatrix::evaluate_polys_over::<8> (row_matrix.rs:82-98)."""
         f, n, B, C_ = polys.field, polys.num_rows(), domain.blowup, polys.num_cols()
+        deg = getattr(polys, "ext_degree", 1)
+        if deg != 1:  # RowMatrix<E> stores base elements: num_base_cols per row (row_matrix.rs:33-41,97)
+            nb = C_ * deg
+            rw = (nb + 7) // 8 * 8
+            out = np.empty((n * B, rw) if f == F64 else (n * B, rw, 2), dtype=np.uint64)
+            check(lib().wg_evaluate_polys_over_ext(f, deg, _ptr_array(polys.columns), C_, n, B, C.c_void_p(domain.offset.ctypes.data),
+                                                   C.c_void_p(out.ctypes.data)))
+            return cls(f, out, rw, nb)
         rw = (C_ + 7) // 8 * 8
         shape = (n * B, rw) if f == F64 else (n * B, rw, 2)
         out = np.empty(shape, dtype=np.uint64)

@@ -25,8 +25,9 @@ def build_trace_commitment(hash_id, traces, domain, want_lde=True, want_polys=Tr
     """traces: list of ColMatrix (one per aggregated trace, all with the same number of rows).
     Returns (list[RowMatrix], MerkleTree, list[ColMatrix]) like the reference."""
     f = traces[0].field
+    deg = getattr(traces[0], "ext_degree", 1)  # E != B: auxiliary trace segments (prover/src/lib.rs:333-334)
     n, B = traces[0].num_rows(), domain.blowup
-    assert all(t.num_rows() == n and t.field == f for t in traces)
+    assert all(t.num_rows() == n and t.field == f and getattr(t, "ext_degree", 1) == deg for t in traces)
     L = n * B
     cols = [c for t in traces for c in t.columns]
     cpt = (C.c_uint32 * len(traces))(*[t.num_cols() for t in traces])
@@ -35,19 +36,22 @@ def build_trace_commitment(hash_id, traces, domain, want_lde=True, want_polys=Tr
     if want_lde:
         ldes = []
         for t in traces:
-            rw = (t.num_cols() + 7) // 8 * 8
+            rw = (t.num_cols() * deg + 7) // 8 * 8
             ldes.append(np.empty((L, rw) if f == F64 else (L, rw, 2), dtype=np.uint64))
     leaves = np.empty((L, 32), dtype=np.uint8)
     nodes = np.empty((L, 32), dtype=np.uint8)
     root = np.empty(32, dtype=np.uint8)
-    check(lib().wg_commit_trace(
-        f, hash_id, n, B, len(traces), cpt, _ptr_array(cols),
-        _ptr_array([c for p in polys for c in p]) if polys else None,
-        _ptr_array(ldes) if ldes else None,
-        C.c_void_p(leaves.ctypes.data), C.c_void_p(nodes.ctypes.data), C.c_void_p(root.ctypes.data)))
+    args = (n, B, len(traces), cpt, _ptr_array(cols),
+            _ptr_array([c for p in polys for c in p]) if polys else None,
+            _ptr_array(ldes) if ldes else None,
+            C.c_void_p(leaves.ctypes.data), C.c_void_p(nodes.ctypes.data), C.c_void_p(root.ctypes.data))
+    if deg != 1:
+        check(lib().wg_commit_trace_ext(f, hash_id, deg, *args))
+    else:
+        check(lib().wg_commit_trace(f, hash_id, *args))
     tree = MerkleTree.from_raw_parts(hash_id, nodes, leaves)
-    lde_m = [RowMatrix(f, d, d.shape[1], t.num_cols()) for d, t in zip(ldes, traces)] if ldes else []
-    poly_m = [ColMatrix(f, p) for p in polys] if polys else []
+    lde_m = [RowMatrix(f, d, d.shape[1], t.num_cols() * deg) for d, t in zip(ldes, traces)] if ldes else []
+    poly_m = [ColMatrix(f, p, deg) for p in polys] if polys else []
     return lde_m, tree, poly_m
 
 
