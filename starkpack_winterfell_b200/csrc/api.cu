@@ -631,7 +631,8 @@ struct DevBufFwd {
 
 // ------------------------------------------------------------------------------------------------ device arithmetic probe
 // Element-wise field ops on the device (tests/test_gpu_parity.py checks them against Python big ints):
-// op 0 add, 1 sub, 2 mul, 16+i mul_root16<false>(a, i), 32+i mul_root16<true>(a, i), 48 as_int (f64 only)
+// op 0 add, 1 sub, 2 mul, 16+i mul_root16<false>(a, i), 32+i mul_root16<true>(a, i), 48 as_int (f64 only),
+// 64+i / 80+i sub_mul_root16<false / true>(a, b, i)
 template <class F>
 __global__ void field_op_kernel(int op, const typename F::T* a, const typename F::T* b, typename F::T* out, uint32_t n) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -648,6 +649,14 @@ __global__ void field_op_kernel(int op, const typename F::T* a, const typename F
 #pragma unroll
     for (int k = 0; k < 16; k++)
       if (op - 32 == k) r = F::template mul_root16<true>(x, k);
+  } else if (op >= 64 && op < 80) {  // (a - b) * w16^(op-64), the butterfly form the NTT kernels use
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if (op - 64 == k) r = F::template sub_mul_root16<false>(x, y, k);
+  } else if (op >= 80 && op < 96) {
+#pragma unroll
+    for (int k = 0; k < 16; k++)
+      if (op - 80 == k) r = F::template sub_mul_root16<true>(x, y, k);
   } else if (op == 48) {
     if (F::kFieldId == 0) {
       uint64_t w;

@@ -87,8 +87,7 @@ __device__ __forceinline__ void radix_ntt(typename F::T (&a)[1 << LR]) {
       for (int k = 0; k < half; k++) {
         T x = a[g + k], y = a[g + k + half];
         a[g + k] = F::add(x, y);
-        T d = F::sub(x, y);
-        a[g + k + half] = (k == 0) ? d : F::template mul_root16<INV>(d, k * (8 / half));
+        a[g + k + half] = F::template sub_mul_root16<INV>(x, y, k * (8 / half));
       }
     }
   }

@@ -63,6 +63,9 @@ def test_device_field_ops_f64(wg):
     for i in range(16):
         assert [int(x) for x in _field_op(wg, F64, 16 + i, a, b)] == [x * pow(2, 12 * i, P64) % P64 for x in A], i
         assert [int(x) for x in _field_op(wg, F64, 32 + i, a, b)] == [x * pow(2, -12 * i, P64) % P64 for x in A], i
+        # the butterfly form the NTT kernels use: (a - b) * w16^(+-i), sign of the shift constants absorbed by the subtraction
+        assert [int(x) for x in _field_op(wg, F64, 64 + i, a, b)] == [(x - y) * pow(2, 12 * i, P64) % P64 for x, y in zip(A, Bv)], i
+        assert [int(x) for x in _field_op(wg, F64, 80 + i, a, b)] == [(x - y) * pow(2, -12 * i, P64) % P64 for x, y in zip(A, Bv)], i
     w = rng.integers(0, 2**64, 4000, dtype=np.uint64)
     assert [int(x) for x in _field_op(wg, F64, 48, w, w)] == [int(x) * rinv % P64 for x in w]
 
@@ -82,6 +85,8 @@ def test_device_field_ops_f128(wg):
     for i in range(16):
         assert un(_field_op(wg, F128, 16 + i, a, b)) == [x * pow(w16, i, q) % q for x in vals], i
         assert un(_field_op(wg, F128, 32 + i, a, b)) == [x * pow(w16, -i, q) % q for x in vals], i
+        assert un(_field_op(wg, F128, 64 + i, a, b)) == [(x - y) * pow(w16, i, q) % q for x, y in zip(vals, bv)], i
+        assert un(_field_op(wg, F128, 80 + i, a, b)) == [(x - y) * pow(w16, -i, q) % q for x, y in zip(vals, bv)], i
 
 
 SIZES = [2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 1 << 14, 1 << 15, 1 << 17]
