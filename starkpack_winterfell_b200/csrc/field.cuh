@@ -306,20 +306,51 @@ struct F128 {
   static WG_HD bool is_zero(T a) { return (a.lo | a.hi) == 0; }
   static WG_HD T canon(T a) { return u128_lt(a, modulus()) ? a : u128_sub(a, modulus()); }
 
+  // Device add / sub / mul are 32-bit carry chains in PTX (the portable C forms compile to 34 / 27 / 145 SASS
+  // instructions, these to 15 / 11 / ~110). -q mod 2^128 = K = 45*2^40 - 1 = (0, 0, 0x2CFF, 0xFFFFFFFF).
   static WG_HD T add(T a, T b) {
+#if defined(__CUDA_ARCH__)
+    // s = a + b (129 bits), t = s + K = s - q mod 2^128; a + b >= q exactly when one of the two additions carries out
+    T r;
+    asm("{\n\t.reg .u32 a0, a1, a2, a3, b0, b1, b2, b3, s0, s1, s2, s3, t0, t1, t2, t3, c;\n\t.reg .pred p;\n\t"
+        "mov.b64 {a0, a1}, %2;\n\tmov.b64 {a2, a3}, %3;\n\tmov.b64 {b0, b1}, %4;\n\tmov.b64 {b2, b3}, %5;\n\t"
+        "add.cc.u32 s0, a0, b0;\n\taddc.cc.u32 s1, a1, b1;\n\taddc.cc.u32 s2, a2, b2;\n\taddc.cc.u32 s3, a3, b3;\n\taddc.u32 c, 0, 0;\n\t"
+        "add.cc.u32 t0, s0, 0xFFFFFFFF;\n\taddc.cc.u32 t1, s1, 0x2CFF;\n\taddc.cc.u32 t2, s2, 0;\n\taddc.cc.u32 t3, s3, 0;\n\taddc.u32 c, c, 0;\n\t"
+        "setp.ne.u32 p, c, 0;\n\t"
+        "selp.u32 s0, t0, s0, p;\n\tselp.u32 s1, t1, s1, p;\n\tselp.u32 s2, t2, s2, p;\n\tselp.u32 s3, t3, s3, p;\n\t"
+        "mov.b64 %0, {s0, s1};\n\tmov.b64 %1, {s2, s3};\n\t}"
+        : "=l"(r.lo), "=l"(r.hi)
+        : "l"(a.lo), "l"(a.hi), "l"(b.lo), "l"(b.hi));
+    return r;
+#else
     uint64_t c;
     T s = u128_add(a, b, c);
     // a,b < q: true sum < 2q. Subtract q when the sum overflowed 2^128 or is >= q.
     if (c || !u128_lt(s, modulus())) s = u128_sub(s, modulus());
     return s;
+#endif
   }
   static WG_HD T sub(T a, T b) {
+#if defined(__CUDA_ARCH__)
+    // d = a - b mod 2^128, then + q under the borrow mask; q = (0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFD300, 1)
+    T r;
+    asm("{\n\t.reg .u32 a0, a1, a2, a3, b0, b1, b2, b3, d0, d1, d2, d3, m, q0, q1;\n\t"
+        "mov.b64 {a0, a1}, %2;\n\tmov.b64 {a2, a3}, %3;\n\tmov.b64 {b0, b1}, %4;\n\tmov.b64 {b2, b3}, %5;\n\t"
+        "sub.cc.u32 d0, a0, b0;\n\tsubc.cc.u32 d1, a1, b1;\n\tsubc.cc.u32 d2, a2, b2;\n\tsubc.cc.u32 d3, a3, b3;\n\tsubc.u32 m, 0, 0;\n\t"
+        "and.b32 q0, m, 1;\n\tand.b32 q1, m, 0xFFFFD300;\n\t"
+        "add.cc.u32 d0, d0, q0;\n\taddc.cc.u32 d1, d1, q1;\n\taddc.cc.u32 d2, d2, m;\n\taddc.u32 d3, d3, m;\n\t"
+        "mov.b64 %0, {d0, d1};\n\tmov.b64 %1, {d2, d3};\n\t}"
+        : "=l"(r.lo), "=l"(r.hi)
+        : "l"(a.lo), "l"(a.hi), "l"(b.lo), "l"(b.hi));
+    return r;
+#else
     T d = u128_sub(a, b);
     if (u128_lt(a, b)) {
       uint64_t c;
       d = u128_add(d, modulus(), c);
     }
     return d;
+#endif
   }
   static WG_HD T neg(T a) { return is_zero(a) ? a : u128_sub(modulus(), a); }
 
@@ -330,6 +361,62 @@ struct F128 {
     return u128_add(l, T{plo, phi}, carry);
   }
   static WG_HD T mul(T a, T b) {
+#if defined(__CUDA_ARCH__)
+    // 256-bit product from sixteen 32x32->64 products: those with i+j even sit on 64-bit boundaries, those with i+j
+    // odd are offset by 32 bits, so each class is summed with 64-bit carry chains and the two sums are merged once.
+    // Reduction (2^128 = K = 45*2^40 - 1 mod q): T = H*2^128 + L  ->  U = L + (H*45 << 40) - H  (< 2^174), its top
+    // 46 bits H2 folded the same way -> V < 2^128 + 2^92, the single carry folded as + K, then one conditional - q.
+    T r;
+    asm("{\n\t.reg .u32 a0, a1, a2, a3, b0, b1, b2, b3, t0, t1, t2, t3, t4, t5, t6, t7;\n\t"
+        ".reg .u32 e0l, e0h, e1l, e1h, e2l, e2h, e3l, e3h, o0l, o0h, o1l, o1h, o2l, o2h, o3l, o3h;\n\t"
+        ".reg .u32 g0, g1, g2, g3, g4, wl, wh, m1, m2, m3, m4, m5, u0, u1, u2, u3, u4, u5, c3, msk, k1, s0, s1, s2, s3;\n\t"
+        ".reg .u64 p00, p01, p02, p03, p10, p11, p12, p13, p20, p21, p22, p23, p30, p31, p32, p33;\n\t"
+        ".reg .u64 E1, E2, E3, O0, O1, O2, O3, w;\n\t.reg .pred p;\n\t"
+        "mov.b64 {a0, a1}, %2;\n\tmov.b64 {a2, a3}, %3;\n\tmov.b64 {b0, b1}, %4;\n\tmov.b64 {b2, b3}, %5;\n\t"
+        "mul.wide.u32 p00, a0, b0;\n\tmul.wide.u32 p01, a0, b1;\n\tmul.wide.u32 p02, a0, b2;\n\tmul.wide.u32 p03, a0, b3;\n\t"
+        "mul.wide.u32 p10, a1, b0;\n\tmul.wide.u32 p11, a1, b1;\n\tmul.wide.u32 p12, a1, b2;\n\tmul.wide.u32 p13, a1, b3;\n\t"
+        "mul.wide.u32 p20, a2, b0;\n\tmul.wide.u32 p21, a2, b1;\n\tmul.wide.u32 p22, a2, b2;\n\tmul.wide.u32 p23, a2, b3;\n\t"
+        "mul.wide.u32 p30, a3, b0;\n\tmul.wide.u32 p31, a3, b1;\n\tmul.wide.u32 p32, a3, b2;\n\tmul.wide.u32 p33, a3, b3;\n\t"
+        // even class: (E3:E2:E1:p00)
+        "add.cc.u64 E1, p02, p11;\n\taddc.cc.u64 E2, p13, p22;\n\taddc.u64 E3, p33, 0;\n\t"
+        "add.cc.u64 E1, E1, p20;\n\taddc.cc.u64 E2, E2, p31;\n\taddc.u64 E3, E3, 0;\n\t"
+        // odd class, 32 bits up: (O3:O2:O1:O0)
+        "add.cc.u64 O0, p01, p10;\n\taddc.cc.u64 O1, p03, p12;\n\taddc.cc.u64 O2, p23, p32;\n\taddc.u64 O3, 0, 0;\n\t"
+        "add.cc.u64 O1, O1, p21;\n\taddc.cc.u64 O2, O2, 0;\n\taddc.u64 O3, O3, 0;\n\t"
+        "add.cc.u64 O1, O1, p30;\n\taddc.cc.u64 O2, O2, 0;\n\taddc.u64 O3, O3, 0;\n\t"
+        "mov.b64 {t0, e0h}, p00;\n\tmov.b64 {e1l, e1h}, E1;\n\tmov.b64 {e2l, e2h}, E2;\n\tmov.b64 {e3l, e3h}, E3;\n\t"
+        "mov.b64 {o0l, o0h}, O0;\n\tmov.b64 {o1l, o1h}, O1;\n\tmov.b64 {o2l, o2h}, O2;\n\tmov.b64 {o3l, o3h}, O3;\n\t"
+        "add.cc.u32 t1, e0h, o0l;\n\taddc.cc.u32 t2, e1l, o0h;\n\taddc.cc.u32 t3, e1h, o1l;\n\taddc.cc.u32 t4, e2l, o1h;\n\t"
+        "addc.cc.u32 t5, e2h, o2l;\n\taddc.cc.u32 t6, e3l, o2h;\n\taddc.u32 t7, e3h, o3l;\n\t"
+        // G = H * 45 (5 limbs)
+        "mul.wide.u32 w, t4, 45;\n\tmov.b64 {g0, wh}, w;\n\t"
+        "mul.wide.u32 w, t5, 45;\n\tmov.b64 {wl, g2}, w;\n\tadd.cc.u32 g1, wl, wh;\n\t"
+        "mul.wide.u32 w, t6, 45;\n\tmov.b64 {wl, g3}, w;\n\taddc.cc.u32 g2, g2, wl;\n\t"
+        "mul.wide.u32 w, t7, 45;\n\tmov.b64 {wl, g4}, w;\n\taddc.cc.u32 g3, g3, wl;\n\taddc.u32 g4, g4, 0;\n\t"
+        // M = G << 40: limbs 1..5
+        "shl.b32 m1, g0, 8;\n\tshf.l.wrap.b32 m2, g0, g1, 8;\n\tshf.l.wrap.b32 m3, g1, g2, 8;\n\tshf.l.wrap.b32 m4, g2, g3, 8;\n\t"
+        "shf.l.wrap.b32 m5, g3, g4, 8;\n\t"
+        // U = L + M - H (6 limbs)
+        "add.cc.u32 u1, t1, m1;\n\taddc.cc.u32 u2, t2, m2;\n\taddc.cc.u32 u3, t3, m3;\n\taddc.cc.u32 u4, m4, 0;\n\taddc.u32 u5, m5, 0;\n\t"
+        "sub.cc.u32 u0, t0, t4;\n\tsubc.cc.u32 u1, u1, t5;\n\tsubc.cc.u32 u2, u2, t6;\n\tsubc.cc.u32 u3, u3, t7;\n\t"
+        "subc.cc.u32 u4, u4, 0;\n\tsubc.u32 u5, u5, 0;\n\t"
+        // second fold: H2 = (u5:u4) < 2^46; G2 = H2 * 45 < 2^52 = (g1:g0); N = G2 << 40 = limbs 1, 2
+        "mul.wide.u32 w, u4, 45;\n\tmov.b64 {g0, wh}, w;\n\tmad.lo.u32 g1, u5, 45, wh;\n\t"
+        "shl.b32 m1, g0, 8;\n\tshf.l.wrap.b32 m2, g0, g1, 8;\n\t"
+        "add.cc.u32 u1, u1, m1;\n\taddc.cc.u32 u2, u2, m2;\n\taddc.cc.u32 u3, u3, 0;\n\taddc.u32 c3, 0, 0;\n\t"
+        "sub.cc.u32 u0, u0, u4;\n\tsubc.cc.u32 u1, u1, u5;\n\tsubc.cc.u32 u2, u2, 0;\n\tsubc.cc.u32 u3, u3, 0;\n\tsubc.u32 c3, c3, 0;\n\t"
+        // third fold: + K under the carry
+        "neg.s32 msk, c3;\n\tand.b32 k1, msk, 0x2CFF;\n\t"
+        "add.cc.u32 u0, u0, msk;\n\taddc.cc.u32 u1, u1, k1;\n\taddc.cc.u32 u2, u2, 0;\n\taddc.u32 u3, u3, 0;\n\t"
+        // canonical: - q when >= q
+        "add.cc.u32 s0, u0, 0xFFFFFFFF;\n\taddc.cc.u32 s1, u1, 0x2CFF;\n\taddc.cc.u32 s2, u2, 0;\n\taddc.cc.u32 s3, u3, 0;\n\taddc.u32 c3, 0, 0;\n\t"
+        "setp.ne.u32 p, c3, 0;\n\t"
+        "selp.u32 u0, s0, u0, p;\n\tselp.u32 u1, s1, u1, p;\n\tselp.u32 u2, s2, u2, p;\n\tselp.u32 u3, s3, u3, p;\n\t"
+        "mov.b64 %0, {u0, u1};\n\tmov.b64 %1, {u2, u3};\n\t}"
+        : "=l"(r.lo), "=l"(r.hi)
+        : "l"(a.lo), "l"(a.hi), "l"(b.lo), "l"(b.hi));
+    return r;
+#else
     // 256-bit schoolbook product w3..w0 (64-bit words)
     uint64_t h00, l00, h01, l01, h10, l10, h11, l11;
     mul64wide(a.lo, b.lo, h00, l00);
@@ -368,6 +455,7 @@ struct F128 {
       t = u128_add(t, T{K, 0}, c2b);
     }
     return canon(t);
+#endif
   }
   // w16^idx, w16 = ROOT^(2^36) (order 16); literals so the compiler folds them at unrolled call sites
   static WG_HD T root16(int idx) {

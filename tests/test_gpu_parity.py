@@ -73,7 +73,11 @@ def test_device_field_ops_f64(wg):
 def test_device_field_ops_f128(wg):
     rng = np.random.default_rng(12)
     q = fx.P128
-    vals = [0, 1, q - 1, q - 2, 2**64 - 1, 2**64, 2**127, q - 2**64] + [int.from_bytes(rng.bytes(16), "little") % q for _ in range(3000)]
+    K = 45 * 2**40 - 1  # 2^128 mod q
+    edge = [0, 1, 2, q - 1, q - 2, 2**64 - 1, 2**64, 2**127, q - 2**64, 2**128 - 2**64, K, K + 1, q - K, 2**96, 2**96 - 1,
+            q - 2**40, (q - 1) // 2, 2**32 - 1, 2**32, (2**32 - 1) * (2**96 + 2**64 + 2**32 + 1) % q]
+    # every edge value meets every edge value (the reversed copy pairs vals[i] with vals[-1-i])
+    vals = [e for e in edge for _ in edge] + [int.from_bytes(rng.bytes(16), "little") % q for _ in range(3000)] + [e for _ in edge for e in edge][::-1]
     a = np.array([(v & fx.MASK, v >> 64) for v in vals], dtype=np.uint64)
     bv = vals[::-1]
     b = np.array([(v & fx.MASK, v >> 64) for v in bv], dtype=np.uint64)
