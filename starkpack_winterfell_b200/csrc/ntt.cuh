@@ -113,7 +113,19 @@ struct FieldCfg<Gl64> {
 #endif
   static constexpr int LOG_TILE = WG_GL_LOG_TILE;  // S*TW <= 2^LOG_TILE elements (64 KB at 13)
   static constexpr int MAX_LOG_TW = 3;
-  static constexpr int PAD_LOG = 3;  // pad unit: 8 elements = 64 B
+  // Shared-memory padding. A 64-bit access is served per half-warp, conflict-free when its 16 lanes fall in 16 different
+  // 8-byte bank pairs. The last register step reads element 8q + r of column w in lane (w, q) = (lane & 3, lane >> 2):
+  //   LAYOUT 0 (index s*TW + w, TW = 4): 4 pad elements per 32 make the q stride 36 = 4 (mod 16)  -> {0,4,8,12} + w
+  //   LAYOUT 1 (index w*SP + s):        1 pad element per 16 and SP = 2 (mod 16) -> {0,8,1,9} + 2w
+  // (8 pad elements per 32 / per 128, the earlier choice, left a 2-way conflict on that step: 20 % of all wavefronts.)
+#ifndef WG_GL_PAD0
+#define WG_GL_PAD0 2
+#endif
+#ifndef WG_GL_L1FINE
+#define WG_GL_L1FINE 1
+#endif
+  static constexpr int PAD_LOG = WG_GL_PAD0;
+  static constexpr bool L1_FINE = WG_GL_L1FINE;
   static constexpr int MIN_BLOCKS = WG_GL_MINB;  // resident 512-thread blocks per SM the kernels are compiled for
 };
 template <>
@@ -122,6 +134,7 @@ struct FieldCfg<F128> {
   static constexpr int LOG_TILE = 13;
   static constexpr int MAX_LOG_TW = 2;
   static constexpr int PAD_LOG = 2;  // 4 elements = 64 B
+  static constexpr bool L1_FINE = false;
   static constexpr int MIN_BLOCKS = 1;
 };
 
@@ -146,11 +159,13 @@ struct PassCfg {
   static constexpr int NT = ITEMS0 >= 512 ? 512 : (ITEMS0 <= 32 ? 32 : ITEMS0);
   // shared-memory index of logical (s, w); padded against bank conflicts of the last register step
   static constexpr int PAD_SHIFT = LAYOUT == 0 ? (LR_LAST + LOG_TW) : 7;
-  static constexpr int SP = S + ((S >> 7) << FC::PAD_LOG) + 1;  // LAYOUT 1 row pitch
+  static constexpr int SP = FC::L1_FINE ? S + (S >> 4) + 2 : S + ((S >> 7) << FC::PAD_LOG) + 1;  // LAYOUT 1 row pitch
   static __host__ __device__ __forceinline__ int phys(int s, int w) {
     if (LAYOUT == 0) {
       int idx = s * TW + w;
       return idx + ((idx >> PAD_SHIFT) << FC::PAD_LOG);
+    } else if (FC::L1_FINE) {
+      return w * SP + s + (s >> 4);
     } else {
       return w * SP + s + ((s >> 7) << FC::PAD_LOG);
     }
