@@ -205,6 +205,24 @@ int wg_fri_commit_layer_dev(int field, int hash, const void* d_evaluations, uint
 int wg_fri_apply_drp_dev(int field, const void* d_transposed, uint64_t rows, uint32_t folding_factor,
                          const void* domain_offset_host, const void* alpha_host, void* d_out, void* stream);
 
+/* ---- multi-GPU LDE with the row-block exchange fused into the kernel ---------------------------------------
+ * One process per GPU. Leaves need whole rows, so the column-sharded LDE has to become row blocks: GPU g hashes rows
+ * [g*L/G, (g+1)*L/G) of every shard. Instead of LDE -> all-to-all, wg_lde_scatter_dev's last pass stores each row
+ * directly into its owner's buffer through peer-mapped pointers (NVLink P2P stores), overlapping the transfer with the
+ * butterflies tile by tile: d_row_blocks[g] is the (L/G) x row_width matrix that receives THIS rank's columns on GPU g
+ * (g = own rank: ordinary local memory). n_owners is a power of two <= 8. The caller orders the hash after the scatter
+ * with any cross-GPU barrier on the stream (starkpack_winterfell_b200/parallel.py uses a 4-byte NCCL all-reduce).
+ * wg_peer_alloc / wg_peer_open export and map such buffers between processes (CUDA IPC; the 64-byte handle travels over
+ * any channel, e.g. torch.distributed.all_gather). */
+#define WG_PEER_HANDLE_BYTES 64
+int wg_peer_alloc(uint64_t bytes, void** d_ptr, uint8_t* handle_out /* WG_PEER_HANDLE_BYTES */);
+int wg_peer_open(const uint8_t* handle, void** d_ptr);
+int wg_peer_close(void* d_ptr);
+int wg_peer_free(void* d_ptr);
+int wg_lde_scatter_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset_host,
+                       uint32_t n_owners, void* const* d_row_blocks, uint64_t row_width, void* d_scratch,
+                       uint64_t scratch_elems, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,6 +25,7 @@ SYMBOLS = [
     "wg_fri_commit_layer", "wg_fri_apply_drp", "wg_fri_commit_layer_dev", "wg_fri_apply_drp_dev",
     "wg_interpolate_poly_ext", "wg_interpolate_poly_with_offset_ext", "wg_evaluate_poly_ext", "wg_evaluate_poly_with_offset_ext",
     "wg_interpolate_columns_ext", "wg_evaluate_polys_over_ext", "wg_commit_trace_ext",
+    "wg_peer_alloc", "wg_peer_open", "wg_peer_close", "wg_peer_free", "wg_lde_scatter_dev",
 ]
 
 
@@ -93,6 +94,11 @@ def lib():
         L.wg_interpolate_columns_ext.argtypes = [i32, u32, vp, u32, u64, vp]
         L.wg_evaluate_polys_over_ext.argtypes = [i32, u32, vp, u32, u64, u64, vp, vp]
         L.wg_commit_trace_ext.argtypes = [i32, i32, u32, u64, u64, u32, vp, vp, vp, vp, vp, vp, vp]
+        L.wg_peer_alloc.argtypes = [u64, vp, vp]
+        L.wg_peer_open.argtypes = [vp, vp]
+        L.wg_peer_close.argtypes = [vp]
+        L.wg_peer_free.argtypes = [vp]
+        L.wg_lde_scatter_dev.argtypes = [i32, vp, u32, u64, u64, vp, u32, vp, u64, vp, u64, vp]
         _lib = L
     return _lib
 

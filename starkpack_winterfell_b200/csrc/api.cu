@@ -378,9 +378,18 @@ static uint64_t lde_scratch_elems(uint32_t n_cols, uint64_t n, uint64_t blowup) 
 template <class F>
 static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, typename F::T offset,
                    typename F::T* d_lde, uint64_t row_width, typename F::T* d_scratch, uint64_t scratch_elems,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, typename F::T* const* d_peers = nullptr, uint32_t n_peers = 0) {
+  // d_peers (multi-GPU): row block g of the result, rows [g*L/G, (g+1)*L/G), is written to d_peers[g] (a buffer of
+  // L/G x row_width elements, usually peer-mapped memory of GPU g) instead of d_lde; see PassArgs::out_peers.
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, blowup));
+  if (n_peers) {
+    if (!d_peers || !is_pow2(n_peers) || n_peers > (uint32_t)PassArgs<F>::MAX_PEERS)
+      return fail(WG_ERR_ARG, "number of row-block owners must be a power of two <= %d", PassArgs<F>::MAX_PEERS);
+    int sa, sb;
+    split_passes(ilog2(n), &sa, &sb);
+    if (((uint64_t)1 << sb) < n_peers) return fail(WG_ERR_UNSUPPORTED, "trace too short for %u row blocks", n_peers);
+  }
   if (F::is_zero(offset)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
   if (row_width < n_cols) return fail(WG_ERR_ARG, "row_width < n_cols");
   if (n_cols == 0) return WG_OK;
@@ -414,6 +423,11 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
     a.pm_w = 0;
     a.pm_lb = pm.lb;
     a.pm_mask = (uint32_t)(n - 1);
+    if (n_peers) {
+      a.n_peers = n_peers;
+      a.peer_shift = (uint32_t)(nb - ilog2(n_peers));
+      for (uint32_t g = 0; g < n_peers; g++) a.out_peers[g] = d_peers[g];
+    }
     const int tw = 1 << pass_log_tw<F>(nb);
     ProfScope ps(PH_LDE_B, stream);
     return launch_pass<F>(1, false, nb, a, dim3(cdiv(row_width, tw), 1, B), stream);
@@ -511,6 +525,11 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
         a.tm_hi = tm.hi;
         a.tm_lb = tm.lb;
         a.tm_mask = (uint32_t)(n - 1);
+      }
+      if (n_peers) {
+        a.n_peers = n_peers;
+        a.peer_shift = (uint32_t)(nb - ilog2(n_peers));
+        for (uint32_t g = 0; g < n_peers; g++) a.out_peers[g] = d_peers[g] + c0;
       }
       const int tw = 1 << pass_log_tw<F>(nb);
       a.nx = cdiv(nc_out, tw);
@@ -1801,6 +1820,60 @@ int wg_commit_trace_ext(int field, int hash, uint32_t ext_degree, uint64_t n_row
   WG_FIELD_DISPATCH(field,
                     h_commit_trace_ext<Gl64>(hash, ext_degree, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out, leaves_out, nodes_out, root_out),
                     h_commit_trace_ext<F128>(hash, ext_degree, n_rows, blowup, n_traces, cols_per_trace, column_ptrs, polys_out, lde_out, leaves_out, nodes_out, root_out));
+}
+
+// ---- multi-GPU: LDE that stores its rows straight into the row-block owners' buffers over NVLink
+int wg_peer_alloc(uint64_t bytes, void** d_ptr, uint8_t* handle_out) {
+  if (!d_ptr || !handle_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, bytes ? bytes : 256);  // a whole allocation of its own: IPC handles name allocations
+  if (e != cudaSuccess) return fail(WG_ERR_NOMEM, "cudaMalloc(%llu): %s", (unsigned long long)bytes, cudaGetErrorString(e));
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail(WG_ERR_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  }
+  static_assert(sizeof(h) == WG_PEER_HANDLE_BYTES, "IPC handle size");
+  memcpy(handle_out, &h, sizeof h);
+  *d_ptr = p;
+  return WG_OK;
+}
+
+int wg_peer_open(const uint8_t* handle, void** d_ptr) {
+  if (!handle || !d_ptr) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  CUDA_TRY(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return WG_OK;
+}
+
+int wg_peer_close(void* d_ptr) {
+  if (!d_ptr) return WG_OK;
+  WG_TRY(ensure_device());
+  CUDA_TRY(cudaIpcCloseMemHandle(d_ptr));
+  return WG_OK;
+}
+
+int wg_peer_free(void* d_ptr) {
+  if (!d_ptr) return WG_OK;
+  WG_TRY(ensure_device());
+  CUDA_TRY(cudaFree(d_ptr));
+  return WG_OK;
+}
+
+int wg_lde_scatter_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset_host,
+                       uint32_t n_owners, void* const* d_row_blocks, uint64_t row_width, void* d_scratch, uint64_t scratch_elems,
+                       void* stream) {
+  if (!offset_host || !d_row_blocks || !d_polys) return fail(WG_ERR_ARG, "null pointer");
+  if (n_owners == 0) return fail(WG_ERR_ARG, "no row-block owners");
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field,
+                    lde_dev<Gl64>((const uint64_t*)d_polys, n_cols, n, blowup, offset_from_internal<Gl64>(offset_host), nullptr, row_width, (uint64_t*)d_scratch, scratch_elems, s, (uint64_t* const*)d_row_blocks, n_owners),
+                    lde_dev<F128>((const u128*)d_polys, n_cols, n, blowup, offset_from_internal<F128>(offset_host), nullptr, row_width, (u128*)d_scratch, scratch_elems, s, (u128* const*)d_row_blocks, n_owners));
 }
 
 }  // extern "C"

@@ -65,6 +65,14 @@ struct PassArgs {
   // zfast = nz > 0: the grid is (gx*nz, gy, 1) and z = blockIdx.x % nz varies fastest, so the nz blocks that read
   // the same input tile (the cosets of one polynomial slice) are co-resident and all but one hit in L2
   uint32_t zfast;
+  // n_peers > 0: the output is scattered over n_peers buffers by transform index j: element j goes to
+  // out_peers[j >> peer_shift] at index j & (2^peer_shift - 1) (everything else as for `out`). This is the multi-GPU
+  // LDE: output row k = j*stride + ... belongs to the GPU that hashes rows [g*L/G, (g+1)*L/G), and the pointers are
+  // peer-mapped (CUDA IPC) buffers on those GPUs, so the pass stores its rows over NVLink while it computes and no
+  // separate all-to-all exists.
+  static constexpr int MAX_PEERS = 8;
+  T* out_peers[MAX_PEERS];
+  uint32_t n_peers, peer_shift;
 };
 
 // ---------------------------------------------------------------------------------------------- radix butterflies
@@ -294,7 +302,8 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
         }
       }
       if (wg < A.nw_out) {
-        T* dst = A.out + out_base + (long long)wg * A.out_wstride;
+        const long long dst_off = out_base + (long long)wg * A.out_wstride;
+        T* dst = A.out + dst_off;
         uint32_t ebase = 0, estep = 0;
         if (A.has_tm) {
           uint32_t f = wg * A.tm_w + y * A.tm_y;
@@ -310,7 +319,12 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
           } else if (A.has_const) {
             v = F::mul(v, A.post_const);
           }
-          dst[(long long)(nat0 + (j << shift_out)) * A.out_jstride] = v;
+          const uint32_t jj = (uint32_t)(nat0 + (j << shift_out));
+          if (A.n_peers) {
+            A.out_peers[jj >> A.peer_shift][dst_off + (long long)(jj & ((1u << A.peer_shift) - 1u)) * A.out_jstride] = v;
+          } else {
+            dst[(long long)jj * A.out_jstride] = v;
+          }
         }
       }
     }
@@ -360,7 +374,13 @@ __global__ void __launch_bounds__(PassCfg<F, LOG_S, LAYOUT>::NT, FieldCfg<F>::MI
         // a tile of zero problems (the LDE's padding columns): the transform of zeros is zeros
         for (int i = threadIdx.x; i < C::S * C::TW; i += C::NT) {
           const uint32_t wg = w0 + (uint32_t)(i & (C::TW - 1));
-          if (wg < A.nw_out) A.out[out_base + (long long)wg * A.out_wstride + (long long)(i >> C::LOG_TW) * A.out_jstride] = F::zero();
+          const uint32_t jj = (uint32_t)(i >> C::LOG_TW);
+          if (wg >= A.nw_out) continue;
+          if (A.n_peers)
+            A.out_peers[jj >> A.peer_shift][out_base + (long long)wg * A.out_wstride +
+                                            (long long)(jj & ((1u << A.peer_shift) - 1u)) * A.out_jstride] = F::zero();
+          else
+            A.out[out_base + (long long)wg * A.out_wstride + (long long)jj * A.out_jstride] = F::zero();
         }
         continue;
       }

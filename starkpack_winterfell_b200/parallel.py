@@ -12,6 +12,11 @@ rows (all columns of all aggregated traces) to form a leaf. Interpolation and LD
   4. the G subtree roots are all-gathered and the top log2(G) levels are computed (redundantly on every rank; the
      result on rank 0 is the commitment). `gather_nodes()` stitches the reference's heap-layout node array.
 
+`DistributedCommitter(..., fused=True)` replaces steps 1b + 2 by ONE kernel: the LDE's last pass stores every row straight
+into its owner's receive buffer through peer-mapped pointers (CUDA IPC, NVLink P2P stores; wg_lde_scatter_dev), so the
+transfer overlaps the butterflies tile by tile, no send buffer exists and NCCL only carries a 4-byte barrier and the
+32-byte roots. The receive buffer has the all-to-all's layout, so steps 3-4 are unchanged and the results are identical.
+
 One process per GPU. All compute goes through a backend with four methods; the product backend is the C ABI
 (`DeviceBackend`); tests/ substitutes a CPU checker backend to exercise the partition / exchange / stitching logic under
 gloo without a GPU.
@@ -83,6 +88,50 @@ class DeviceBackend:
                                C.c_void_p(lde.data_ptr()), rw, C.c_void_p(scratch.data_ptr()), int(se), self._stream()))
         return polys, lde
 
+    # ---- fused LDE + exchange ------------------------------------------------------------------------------------
+    def peer_alloc(self, nbytes):
+        """-> (device pointer, 64-byte IPC handle) of a fresh allocation that other ranks can map."""
+        ptr = C.c_void_p()
+        handle = (C.c_uint8 * 64)()
+        check(lib().wg_peer_alloc(int(nbytes), C.byref(ptr), handle))
+        return ptr.value, bytes(handle)
+
+    def peer_open(self, handle):
+        ptr = C.c_void_p()
+        check(lib().wg_peer_open((C.c_uint8 * 64).from_buffer_copy(handle), C.byref(ptr)))
+        return ptr.value
+
+    def peer_close(self, ptr):
+        check(lib().wg_peer_close(C.c_void_p(ptr)))
+
+    def peer_free(self, ptr):
+        check(lib().wg_peer_free(C.c_void_p(ptr)))
+
+    def wrap(self, ptr, shape, dtype=torch.int64):
+        """torch view of raw device memory (no copy, no ownership)."""
+        n = 1
+        for d in shape:
+            n *= d
+
+        class _Raw:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<i8" if dtype == torch.int64 else "|u1", "data": (ptr, False), "version": 2}
+
+        return torch.as_tensor(_Raw(), device=self.device).view(shape)
+
+    def interpolate_lde_scatter(self, cols, n, blowup, row_block_ptrs):
+        """cols [c, n, w] -> polys; LDE rows go to row_block_ptrs[g] (owner g's (L/G) x rw matrix for this rank)."""
+        c = cols.shape[0]
+        rw = (c + 7) // 8 * 8
+        polys = torch.empty_like(cols)
+        se = max(lib().wg_interpolate_scratch_elems(self.field, c, n), lib().wg_lde_scratch_elems(self.field, c, n, blowup))
+        scratch = self.empty((max(int(se), 1), self.w))
+        check(lib().wg_interpolate_columns_dev(self.field, C.c_void_p(cols.data_ptr()), c, n, C.c_void_p(polys.data_ptr()),
+                                               C.c_void_p(scratch.data_ptr()), int(se), self._stream()))
+        ptrs = (C.c_void_p * len(row_block_ptrs))(*row_block_ptrs)
+        check(lib().wg_lde_scatter_dev(self.field, C.c_void_p(polys.data_ptr()), c, n, blowup, C.c_void_p(self._offset.ctypes.data),
+                                       len(row_block_ptrs), ptrs, rw, C.c_void_p(scratch.data_ptr()), int(se), self._stream()))
+        return polys
+
     def hash_rows(self, mats, elems, rows):
         """mats: list of [rows, rw_i, w] int64 row blocks; elems[i] real columns of block i -> leaves [rows, 32]"""
         k = len(mats)
@@ -100,8 +149,10 @@ class DeviceBackend:
 
 
 class DistributedCommitter:
-    def __init__(self, backend, n_rows, blowup, total_cols, group=None):
+    def __init__(self, backend, n_rows, blowup, total_cols, group=None, fused=False):
         self.b, self.n, self.blowup, self.total_cols, self.group = backend, n_rows, blowup, total_cols, group
+        self.fused = fused
+        self._recv_ptr = None
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         assert self.world & (self.world - 1) == 0, "number of ranks must be a power of two"
@@ -117,18 +168,28 @@ class DistributedCommitter:
         G, L = self.world, self.L
         rows = L // G
         assert local_cols.shape[0] == self.col_count
-        self.polys, self.lde = self.b.interpolate_lde(local_cols, self.n, self.blowup)
-        w = self.lde.shape[2]
         rws = [(c + 7) // 8 * 8 for _, c in self.shards]
-        # --- the one exchange: column shards -> row blocks
-        send = self.lde.reshape(-1)
-        recv = self.b.empty((sum(rows * r * w for r in rws),))
-        in_splits = [rows * rws[self.rank] * w] * G
-        out_splits = [rows * r * w for r in rws]
-        if G > 1:
-            dist.all_to_all_single(recv, send, out_splits, in_splits, group=self.group)
+        if self.fused and G > 1:
+            w = local_cols.shape[2]
+            recv = self._fused_setup(rows, rws, w)
+            # owner g's slot for MY columns: after the matrices of ranks 0..rank-1
+            off = sum(rows * r * w for r in rws[: self.rank]) * 8
+            self.polys = self.b.interpolate_lde_scatter(local_cols, self.n, self.blowup, [p + off for p in self._peer_ptrs])
+            self.lde = None
+            # every rank's rows have landed once every rank's LDE kernel has finished: a stream-ordered barrier
+            dist.all_reduce(self._token, group=self.group)
         else:
-            recv.copy_(send)
+            self.polys, self.lde = self.b.interpolate_lde(local_cols, self.n, self.blowup)
+            w = self.lde.shape[2]
+            # --- the one exchange: column shards -> row blocks
+            send = self.lde.reshape(-1)
+            recv = self.b.empty((sum(rows * r * w for r in rws),))
+            in_splits = [rows * rws[self.rank] * w] * G
+            out_splits = [rows * r * w for r in rws]
+            if G > 1:
+                dist.all_to_all_single(recv, send, out_splits, in_splits, group=self.group)
+            else:
+                recv.copy_(send)
         mats, off = [], 0
         for r in rws:
             mats.append(recv[off: off + rows * r * w].view(rows, r, w))
@@ -146,6 +207,34 @@ class DistributedCommitter:
             return bytes(self.top_nodes[1].cpu().numpy())
         self.top_nodes = self.local_nodes[:1]
         return bytes(my_root.cpu().numpy())
+
+    def _fused_setup(self, rows, rws, w):
+        """receive buffer [sum_r rows*rws[r]*w] int64 in its own allocation, mapped into every rank (done once)."""
+        if self._recv_ptr is None:
+            G = self.world
+            self._recv_elems = sum(rows * r * w for r in rws)
+            self._recv_ptr, handle = self.b.peer_alloc(self._recv_elems * 8)
+            mine = torch.tensor(list(handle), dtype=torch.uint8, device=self.b.device)
+            allh = [torch.empty_like(mine) for _ in range(G)]
+            dist.all_gather(allh, mine, group=self.group)
+            self._peer_ptrs = []
+            for g in range(G):
+                self._peer_ptrs.append(self._recv_ptr if g == self.rank else self.b.peer_open(bytes(allh[g].cpu().numpy().tobytes())))
+            self._token = torch.zeros(1, dtype=torch.int32, device=self.b.device)
+            self._recv = self.b.wrap(self._recv_ptr, (self._recv_elems,))
+        return self._recv
+
+    def close(self):
+        """unmap the peers' buffers and free this rank's (all ranks first stop using them: collective)."""
+        if self._recv_ptr is not None:
+            torch.cuda.synchronize(self.b.device)
+            dist.barrier(group=self.group)
+            for g, p in enumerate(self._peer_ptrs):
+                if g != self.rank:
+                    self.b.peer_close(p)
+            dist.barrier(group=self.group)
+            self.b.peer_free(self._recv_ptr)
+            self._recv_ptr = None
 
     def gather_nodes(self):
         """Global heap-layout node array on every rank (verification / handing the tree to a CPU prover)."""
