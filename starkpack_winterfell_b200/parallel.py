@@ -41,6 +41,18 @@ def split_columns(total_cols, world):
     return out
 
 
+def split_chunks(cols, k):
+    """cut `cols` columns into k chunks whose sizes are multiples of 8 except possibly the last non-empty one (the LDE
+    pads every matrix to a multiple of 8 columns and pad columns are not hashed). -> list of k (start, count)."""
+    per = ((cols + k - 1) // k + 7) // 8 * 8
+    out, s = [], 0
+    for _ in range(k):
+        c = min(per, cols - s)
+        out.append((s, max(c, 0)))
+        s += max(c, 0)
+    return out
+
+
 def stitch_nodes(local_nodes, top_nodes, world):
     """local_nodes[g]: [L/G, 32] heap layout of rank g's subtree; top_nodes: [G, 32] heap layout of the tree over the G
     subtree roots. Returns the global [L, 32] heap-layout array of crypto/src/merkle/mod.rs:350-374."""
@@ -73,6 +85,27 @@ class DeviceBackend:
 
     def empty(self, shape, dtype=torch.int64):
         return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def interpolate(self, cols, n):
+        c = cols.shape[0]
+        polys = torch.empty_like(cols)
+        se = int(lib().wg_interpolate_scratch_elems(self.field, c, n))
+        scratch = self.empty((max(se, 1), self.w))
+        check(lib().wg_interpolate_columns_dev(self.field, C.c_void_p(cols.data_ptr()), c, n, C.c_void_p(polys.data_ptr()),
+                                               C.c_void_p(scratch.data_ptr()), se, self._stream()))
+        return polys
+
+    def lde(self, polys, n, blowup, out=None, scratch=None):
+        """polys [c, n, w] -> row-major LDE [n*blowup, 8*ceil(c/8), w] (into `out` when given)"""
+        c = polys.shape[0]
+        rw = (c + 7) // 8 * 8
+        lde = self.empty((n * blowup, rw, self.w)) if out is None else out
+        se = int(lib().wg_lde_scratch_elems(self.field, c, n, blowup))
+        if scratch is None:
+            scratch = self.empty((max(se, 1), self.w))
+        check(lib().wg_lde_dev(self.field, C.c_void_p(polys.data_ptr()), c, n, blowup, C.c_void_p(self._offset.ctypes.data),
+                               C.c_void_p(lde.data_ptr()), rw, C.c_void_p(scratch.data_ptr()), se, self._stream()))
+        return lde
 
     def interpolate_lde(self, cols, n, blowup):
         """cols: [c, n, w] int64 -> (polys [c, n, w], lde [n*blowup, rw, w])"""
@@ -149,9 +182,12 @@ class DeviceBackend:
 
 
 class DistributedCommitter:
-    def __init__(self, backend, n_rows, blowup, total_cols, group=None, fused=False):
+    def __init__(self, backend, n_rows, blowup, total_cols, group=None, fused=False, pipeline=0):
+        """fused: the LDE stores rows into the owners' buffers itself (P2P). pipeline = K > 1: the shard is LDE'd in K
+        column chunks and chunk k's all-to-all (NCCL, its own stream) runs under chunk k+1's LDE."""
         self.b, self.n, self.blowup, self.total_cols, self.group = backend, n_rows, blowup, total_cols, group
         self.fused = fused
+        self.pipeline = pipeline
         self._recv_ptr = None
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
@@ -178,6 +214,8 @@ class DistributedCommitter:
             self.lde = None
             # every rank's rows have landed once every rank's LDE kernel has finished: a stream-ordered barrier
             dist.all_reduce(self._token, group=self.group)
+        elif self.pipeline > 1 and G > 1:
+            return self._commit_pipelined(local_cols)
         else:
             self.polys, self.lde = self.b.interpolate_lde(local_cols, self.n, self.blowup)
             w = self.lde.shape[2]
@@ -207,6 +245,65 @@ class DistributedCommitter:
             return bytes(self.top_nodes[1].cpu().numpy())
         self.top_nodes = self.local_nodes[:1]
         return bytes(my_root.cpu().numpy())
+
+    def _finish(self, mats, elems, rows):
+        G = self.world
+        self.row_block = mats
+        self.leaves = self.b.hash_rows(mats, elems, rows)
+        self.local_nodes = self.b.merkle(self.leaves)
+        my_root = self.local_nodes[1].contiguous()
+        roots = [torch.empty_like(my_root) for _ in range(G)]
+        dist.all_gather(roots, my_root, group=self.group)
+        self.top_nodes = self.b.merkle(torch.stack(roots).contiguous())
+        return bytes(self.top_nodes[1].cpu().numpy())
+
+    def _commit_pipelined(self, local_cols):
+        """Column chunks: LDE of chunk k+1 overlaps the all-to-all of chunk k. Every rank cuts its shard into the same
+        number K of chunks (multiples of 8 columns except the last), so the K collectives pair up; the leaf kernel reads
+        the G*K received matrices in global column order (rank-major, then chunk)."""
+        G, L, K = self.world, self.L, self.pipeline
+        rows = L // G
+        w = local_cols.shape[2]
+        chunks = [split_chunks(c, K) for _, c in self.shards]  # per rank: list of (start, count), count may be 0
+        self.polys = self.b.interpolate(local_cols, self.n)
+        self.lde = None
+        on_gpu = local_cols.is_cuda
+        if on_gpu:
+            comm = torch.cuda.Stream(device=local_cols.device)
+            cur = torch.cuda.current_stream(local_cols.device)
+        recvs, keep = {}, []
+        for k in range(K):
+            if all(chunks[g][k][1] == 0 for g in range(G)):
+                continue
+            s0, cnt = chunks[self.rank][k]
+            rws_k = [(chunks[g][k][1] + 7) // 8 * 8 for g in range(G)]
+            send = self.b.lde(self.polys[s0: s0 + cnt], self.n, self.blowup).reshape(-1) if cnt else self.b.empty((0,))
+            recv = self.b.empty((sum(rows * r * w for r in rws_k),))
+            splits = ([rows * r * w for r in rws_k], [rows * rws_k[self.rank] * w] * G)
+            if on_gpu:
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                with torch.cuda.stream(comm):
+                    comm.wait_event(ev)
+                    dist.all_to_all_single(recv, send, splits[0], splits[1], group=self.group)
+                    send.record_stream(comm)
+                    recv.record_stream(comm)
+            else:
+                dist.all_to_all_single(recv, send, splits[0], splits[1], group=self.group)
+            keep.append(send)
+            recvs[k] = (recv, rws_k)
+        if on_gpu:
+            cur.wait_stream(comm)
+        mats, elems = [], []
+        for g in range(G):
+            for k in range(K):
+                if chunks[g][k][1] == 0:
+                    continue
+                recv, rws_k = recvs[k]
+                off = sum(rows * r * w for r in rws_k[:g])
+                mats.append(recv[off: off + rows * rws_k[g] * w].view(rows, rws_k[g], w))
+                elems.append(chunks[g][k][1])
+        return self._finish(mats, elems, rows)
 
     def _fused_setup(self, rows, rws, w):
         """receive buffer [sum_r rows*rws[r]*w] int64 in its own allocation, mapped into every rank (done once)."""

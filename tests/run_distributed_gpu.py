@@ -24,19 +24,19 @@ def main():
         full = fx.synth_f64(9, total_cols, n) if field == 0 else fx.synth_f128(9, total_cols, n)
         be = DeviceBackend(field, hash_id, dev)
         # fused: the LDE stores rows into the owners' buffers over NVLink (CUDA IPC peer pointers), no all-to-all
-        for fused in (False, True):
-            run_one(be, field, hash_id, n, blowup, total_cols, full, dev, fused)
+        for fused, pipeline in ((False, 0), (True, 0), (False, 2), (False, 4)):
+            run_one(be, field, hash_id, n, blowup, total_cols, full, dev, fused, pipeline)
     dist.barrier()
     if dist.get_rank() == 0:
         print("DISTRIBUTED_OK")
     dist.destroy_process_group()
 
 
-def run_one(be, field, hash_id, n, blowup, total_cols, full, dev, fused):
+def run_one(be, field, hash_id, n, blowup, total_cols, full, dev, fused, pipeline):
     from starkpack_winterfell_b200.parallel import DistributedCommitter
 
     if True:
-        dc = DistributedCommitter(be, n, blowup, total_cols, fused=fused)
+        dc = DistributedCommitter(be, n, blowup, total_cols, fused=fused, pipeline=pipeline)
         a = np.ascontiguousarray(full[dc.col_start: dc.col_start + dc.col_count]).view(np.int64)
         cols = torch.from_numpy(a[..., None] if field == 0 else a).to(dev)
         root = dc.commit(cols)
@@ -47,7 +47,7 @@ def run_one(be, field, hash_id, n, blowup, total_cols, full, dev, fused):
             want = oracle.commit_trace(field, hash_id, [full], blowup, want=("nodes",))
             assert np.array_equal(nodes, want["nodes"]), "stitched nodes differ from the oracle"
             assert root == bytes(want["root"])
-        if fused:
+        if fused or pipeline:
             root2 = dc.commit(cols)  # buffers reused: a second commit must give the same tree
             assert root2 == root
         dc.close()

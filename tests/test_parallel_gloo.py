@@ -36,6 +36,19 @@ class OracleBackend:
         r = self.o.commit_trace(self.field, self.hash_id, [self._np(cols)], blowup, want=("polys", "lde"))
         return self._t(r["polys"][0]), self._t(r["lde"][0])
 
+    def interpolate(self, cols, n):
+        return self._t(np.stack([self.o.interpolate_poly(self.field, c) for c in self._np(cols)]))
+
+    def lde(self, polys, n, blowup, out=None, scratch=None):
+        p = self._np(polys)
+        off = np.array([(7 << 64) % fx.P64], dtype=np.uint64) if self.field == 0 else np.array([3, 0], dtype=np.uint64)
+        cols = [self.o.evaluate_poly_with_offset(self.field, c, off, blowup) for c in p]
+        rw = (len(cols) + 7) // 8 * 8
+        m = np.zeros((n * blowup, rw) + ((2,) if self.field == 1 else ()), dtype=np.uint64)
+        for i, c in enumerate(cols):
+            m[:, i] = c
+        return self._t(m)
+
     def hash_rows(self, mats, elems, rows):
         return torch.from_numpy(self.o.hash_comb_rows(self.field, self.hash_id, [self._np(m) for m in mats], elems))
 
@@ -43,7 +56,7 @@ class OracleBackend:
         return torch.from_numpy(self.o.merkle_nodes(self.hash_id, leaves.numpy()))
 
 
-def _worker(rank, world, port, field, hash_id, n, blowup, total_cols, seed, q):
+def _worker(rank, world, port, field, hash_id, n, blowup, total_cols, seed, q, pipeline=0):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -52,7 +65,7 @@ def _worker(rank, world, port, field, hash_id, n, blowup, total_cols, seed, q):
 
         full = fx.synth_f64(seed, total_cols, n) if field == 0 else fx.synth_f128(seed, total_cols, n)
         be = OracleBackend(field, hash_id)
-        dc = DistributedCommitter(be, n, blowup, total_cols)
+        dc = DistributedCommitter(be, n, blowup, total_cols, pipeline=pipeline)
         local = be._t(full[dc.col_start: dc.col_start + dc.col_count])
         root = dc.commit(local)
         nodes = dc.gather_nodes().numpy()
@@ -71,18 +84,21 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("world,field,hash_id,n,blowup,total_cols", [
-    (2, 0, 0, 64, 8, 10),    # even split 5/5
-    (2, 0, 0, 32, 4, 21),    # uneven widths: 11 -> rw 16, 10 -> rw 16
-    (2, 0, 1, 32, 2, 9),     # 5 -> rw 8, 4 -> rw 8, SHA3
-    (4, 1, 0, 16, 8, 6),     # f128, shards of 2,2,1,1 columns
-    (2, 0, 0, 16, 8, 17),    # 9 -> rw 16, 8 -> rw 8 (different padded widths across ranks)
+@pytest.mark.parametrize("world,field,hash_id,n,blowup,total_cols,pipeline", [
+    (2, 0, 0, 64, 8, 10, 0),    # even split 5/5
+    (2, 0, 0, 32, 4, 21, 0),    # uneven widths: 11 -> rw 16, 10 -> rw 16
+    (2, 0, 1, 32, 2, 9, 0),     # 5 -> rw 8, 4 -> rw 8, SHA3
+    (4, 1, 0, 16, 8, 6, 0),     # f128, shards of 2,2,1,1 columns
+    (2, 0, 0, 16, 8, 17, 0),    # 9 -> rw 16, 8 -> rw 8 (different padded widths across ranks)
+    (2, 0, 0, 16, 8, 37, 2),    # pipelined exchange: chunks 16+3 / 16+2
+    (2, 0, 0, 16, 4, 21, 4),    # 11 -> chunks 8+3+0+0, 10 -> 8+2+0+0 (empty chunks skipped on every rank)
+    (4, 1, 0, 16, 8, 6, 2),     # f128, single-column shards: second chunk empty everywhere
 ])
-def test_distributed_commit_matches_single_process(oracle, world, field, hash_id, n, blowup, total_cols):
+def test_distributed_commit_matches_single_process(oracle, world, field, hash_id, n, blowup, total_cols, pipeline):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, field, hash_id, n, blowup, total_cols, 77, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, field, hash_id, n, blowup, total_cols, 77, q, pipeline)) for r in range(world)]
     for p in procs:
         p.start()
     root, nodes, leaves = q.get(timeout=120)
@@ -101,3 +117,8 @@ def test_split_and_stitch_helpers():
 
     assert split_columns(100, 8) == [(0, 13), (13, 13), (26, 13), (39, 13), (52, 12), (64, 12), (76, 12), (88, 12)]
     assert split_columns(256, 4) == [(0, 64), (64, 64), (128, 64), (192, 64)]
+    from starkpack_winterfell_b200.parallel import split_chunks
+
+    assert split_chunks(128, 4) == [(0, 32), (32, 32), (64, 32), (96, 32)]
+    assert split_chunks(13, 4) == [(0, 8), (8, 5), (13, 0), (13, 0)]
+    assert split_chunks(50, 2) == [(0, 32), (32, 18)]
