@@ -134,6 +134,7 @@ struct FieldCfg<Gl64> {
 #endif
   static constexpr int PAD_LOG = WG_GL_PAD0;
   static constexpr bool L1_FINE = WG_GL_L1FINE;
+  static constexpr bool SKIP_DEAD = false;
   static constexpr int MIN_BLOCKS = WG_GL_MINB;  // resident 512-thread blocks per SM the kernels are compiled for
 };
 template <>
@@ -143,6 +144,7 @@ struct FieldCfg<F128> {
   static constexpr int MAX_LOG_TW = 2;
   static constexpr int PAD_LOG = 2;  // 4 elements = 64 B
   static constexpr bool L1_FINE = false;
+  static constexpr bool SKIP_DEAD = true;  // 2-column fib traces fill half a tile (BASELINE configs 1 and 4)
   static constexpr int MIN_BLOCKS = 1;
 };
 
@@ -229,9 +231,20 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
     const int m_rest = q & ((1 << LOGP) - 1);
     const int s0 = (blk << LOGPP) + m_rest;  // element r lives at s0 + (r << LOGP)
     const uint32_t wg = w0 + (uint32_t)w;
+    // Problems past nw_in are all-zero inputs (the LDE's padding columns inside a partly filled tile: the 2-column
+    // f128 traces fill half a tile): their transform is zero, so they are neither loaded nor transformed nor exchanged;
+    // the last step just stores zeros. In every step but the last of a contiguous pass a warp works on one problem,
+    // so the skipped work is skipped by whole warps.
+    // (Compiled in per field, FieldCfg::SKIP_DEAD: the Goldilocks configurations fill their tiles, and the extra
+    // predicate costs the 2^22 x 100 commit 2.8 %.)
+    const bool in_range = wg < A.nw_in;
+    const bool live = C::FC::SKIP_DEAD ? in_range : true;
     T a[R];
-    if (FIRST) {
-      if (wg < A.nw_in) {
+    if (FIRST ? !in_range : (C::FC::SKIP_DEAD && !in_range)) {
+#pragma unroll
+      for (int r = 0; r < R; r++) a[r] = F::zero();
+    } else if (FIRST) {
+      {
         const T* src = A.in + in_base + (long long)wg * A.in_wstride;
 #pragma unroll
         for (int r = 0; r < R; r++) a[r] = src[(long long)(s0 + (r << LOGP)) * A.in_sstride];
@@ -255,16 +268,13 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
 #pragma unroll
           for (int r = 0; r < R; r++) a[r] = F::mul(a[r], qtab[s0 + (r << LOGP)]);
         }
-      } else {
-#pragma unroll
-        for (int r = 0; r < R; r++) a[r] = F::zero();
       }
     } else {
 #pragma unroll
       for (int r = 0; r < R; r++) a[r] = tile[C::phys(s0 + (r << LOGP), w)];
     }
 
-    radix_ntt<F, LR, INV>(a);
+    if (live) radix_ntt<F, LR, INV>(a);
 
     if (!LAST) {
       // The block's first step 0 runs while the shared twiddle table is still being filled (its loads overlap the
@@ -272,11 +282,13 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
       // With NITEMS >= NT every thread runs the same number of item iterations, so the barrier is uniform.
       if (FIRST && tws_sync && NITEMS >= C::NT && item == (int)threadIdx.x) __syncthreads();
       // twiddle w_{2^LOGPP}^(m_rest*j) from this step's [j][m_rest] sub-table; then scatter digit j
+      if (live) {
 #pragma unroll
-      for (int j = 0; j < R; j++) {
-        T v = a[j];
-        if (j > 0) v = F::mul(v, tws[C::tws_off(U) + (j << LOGP) + m_rest]);
-        tile[C::phys(s0 + (j << LOGP), w)] = v;
+        for (int j = 0; j < R; j++) {
+          T v = a[j];
+          if (j > 0) v = F::mul(v, tws[C::tws_off(U) + (j << LOGP) + m_rest]);
+          tile[C::phys(s0 + (j << LOGP), w)] = v;
+        }
       }
     } else {
       // natural output index: digits j_0 (most significant in blk) ... j_{U-1}, then this step's j
@@ -313,7 +325,9 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
 #pragma unroll
         for (int j = 0; j < R; j++) {
           T v = a[j];
-          if (A.has_tm) {
+          if (!live) {
+            // zero stays zero
+          } else if (A.has_tm) {
             uint32_t e = (ebase + (uint32_t)j * estep) & A.tm_mask;
             v = F::mul(v, table2<F>(A.tm_lo, A.tm_hi, A.tm_lb, e));
           } else if (A.has_const) {
