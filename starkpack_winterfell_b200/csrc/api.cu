@@ -449,7 +449,11 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
   // q^m2, q = t_z * w_n^j1, which carries both the low half of the coset shift and the inter-pass twiddle; pass A' is
   // then left with the direct table t_z^(N2*m1). Otherwise pass A' applies shift and twiddle through two-level tables.
   const size_t smem_b = ntt_pass_smem<F>(1, nb) + (sizeof(T) << nb);
-  const bool use_q = pm.lb == nb && env_int("WG_LDE_Q", 1) && smem_b * FieldCfg<F>::MIN_BLOCKS <= SMEM_PER_SM;
+  // 0: never, 1: only when the table fits at the compiled residency, 2 (default): whenever it fits. At 2^12-point passes
+  // (2^23, 2^24 rows) the table leaves room for one block per SM only, and that is still the faster plan: 2^24 x 32
+  // columns 175.5 -> 148.2 ms (strided pass 74.2 -> 51.3 ms: one table product per element instead of four).
+  const int q_mode = env_int("WG_LDE_Q", 2);
+  const bool use_q = pm.lb == nb && q_mode && smem_b * (q_mode == 2 ? 1 : FieldCfg<F>::MIN_BLOCKS) <= SMEM_PER_SM;
   const unsigned walk_a = (unsigned)env_int("WG_WALK_A", 1), walk_b = (unsigned)env_int("WG_WALK_B", 13);
   for (uint64_t c0 = 0; c0 < row_width; c0 += chunk) {
     const uint32_t nc_out = (uint32_t)((row_width - c0) < chunk ? (row_width - c0) : chunk);  // incl. pad columns
