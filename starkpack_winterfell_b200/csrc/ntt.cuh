@@ -120,6 +120,11 @@ struct FieldCfg<Gl64> {
 #define WG_GL_MINB 2
 #endif
   static constexpr int LOG_TILE = WG_GL_LOG_TILE;  // S*TW <= 2^LOG_TILE elements (64 KB at 13)
+#ifndef WG_GL_LOG_TILE12
+#define WG_GL_LOG_TILE12 14
+#endif
+  // 2^12-point passes (2^23, 2^24 rows) get 128 KB tiles: 4 problems per tile keep the global pieces at 32 bytes
+  static constexpr __host__ __device__ int log_tile(int log_s) { return log_s >= 12 ? WG_GL_LOG_TILE12 : LOG_TILE; }
   static constexpr int MAX_LOG_TW = 3;
   // Shared-memory padding. A 64-bit access is served per half-warp, conflict-free when its 16 lanes fall in 16 different
   // 8-byte bank pairs. The last register step reads element 8q + r of column w in lane (w, q) = (lane & 3, lane >> 2):
@@ -141,6 +146,7 @@ template <>
 struct FieldCfg<F128> {
   static constexpr int MAXLR = 3;
   static constexpr int LOG_TILE = 13;
+  static constexpr __host__ __device__ int log_tile(int) { return LOG_TILE; }
   static constexpr int MAX_LOG_TW = 2;
   static constexpr int PAD_LOG = 2;  // 4 elements = 64 B
   static constexpr bool L1_FINE = false;
@@ -153,7 +159,7 @@ struct PassCfg {
   typedef FieldCfg<F> FC;
   static constexpr int MAXLR = FC::MAXLR;
   static constexpr int NSTEPS = (LOG_S + MAXLR - 1) / MAXLR;
-  static constexpr int LOG_TW = (FC::LOG_TILE - LOG_S) < FC::MAX_LOG_TW ? (FC::LOG_TILE - LOG_S) : FC::MAX_LOG_TW;
+  static constexpr int LOG_TW = (FC::log_tile(LOG_S) - LOG_S) < FC::MAX_LOG_TW ? (FC::log_tile(LOG_S) - LOG_S) : FC::MAX_LOG_TW;
   static constexpr int TW = 1 << LOG_TW;
   static constexpr int S = 1 << LOG_S;
   static constexpr __host__ __device__ int lr(int u) { return u < NSTEPS - 1 ? MAXLR : LOG_S - MAXLR * (NSTEPS - 1); }

@@ -19,7 +19,7 @@ constexpr size_t SMEM_PER_SM = 227 * 1024;
 
 template <class F>
 inline int pass_log_tw(int log_s) {
-  int l = FieldCfg<F>::LOG_TILE - log_s;
+  int l = FieldCfg<F>::log_tile(log_s) - log_s;
   return l < FieldCfg<F>::MAX_LOG_TW ? l : FieldCfg<F>::MAX_LOG_TW;
 }
 
