@@ -23,6 +23,7 @@ ap.add_argument("--cfg5-log-rows", type=int, default=0, help="0: skip cfg5")
 ap.add_argument("--cfg4-log-rows", type=int, default=20)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--pipeline", type=int, default=0, help="K > 1: LDE in K column chunks, chunk k's all-to-all under chunk k+1's LDE")
+ap.add_argument("--auto", type=int, default=0, help="1: DistributedCommitter.auto picks the form of the exchange")
 ap.add_argument("--fused", type=int, default=0, help="1: LDE stores rows into the owners' buffers over NVLink (no all-to-all)")
 args = ap.parse_args()
 local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -59,7 +60,7 @@ def timed(dc, cols, name, n, total_cols, esize):
         print(json.dumps({"config": name, "n_gpus": G, "rows": n, "total_cols": total_cols, "gpu_ms_min": ts[0], "gpu_ms_median": ts[len(ts) // 2],
                           "lde_rows_per_s": L / (ts[0] * 1e-3), "algorithmic_bytes": alg, "hbm_gbs_per_gpu": alg / G / (ts[0] * 1e-3) / 1e9,
                           "exchange_bytes_sent_per_gpu": (L // G) * (G - 1) * ((dc.col_count + 7) // 8 * 8) * esize,
-                          "exchange": "fused into the LDE pass (P2P stores)" if args.fused else (f"NCCL all-to-all in {args.pipeline} column chunks under the LDE" if args.pipeline > 1 else "NCCL all-to-all"), "root": root.hex()}), flush=True)
+                          "exchange": "fused into the LDE pass (P2P stores)" if dc.fused else (f"NCCL all-to-all in {dc.pipeline} column chunks under the LDE" if dc.pipeline > 1 else "NCCL all-to-all"), "root": root.hex()}), flush=True)
     return root
 
 
@@ -67,7 +68,7 @@ def timed(dc, cols, name, n, total_cols, esize):
 n = 1 << args.cfg4_log_rows
 if 16 >= G:
     be = DeviceBackend(1, 0, dev)
-    dc = DistributedCommitter(be, n, B, 16, fused=bool(args.fused), pipeline=args.pipeline)
+    dc = DistributedCommitter.auto(be, n, B, 16) if args.auto else DistributedCommitter(be, n, B, 16, fused=bool(args.fused), pipeline=args.pipeline)
     traces = np.concatenate([fx.fib_trace_f128(n, start=(t + 1, t + 1)) for t in range(8)], axis=0)
     mine = np.ascontiguousarray(traces[dc.col_start: dc.col_start + dc.col_count]).view(np.int64).reshape(dc.col_count, n, 2)
     root = timed(dc, torch.from_numpy(mine).to(dev), "cfg4 starkpack 8 x fib f128 Blake3_256, column-sharded", n, 16, 16)
@@ -87,7 +88,7 @@ if args.cfg5_log_rows:
     n = 1 << args.cfg5_log_rows
     C5 = 256
     be = DeviceBackend(0, 0, dev)
-    dc = DistributedCommitter(be, n, B, C5, fused=bool(args.fused), pipeline=args.pipeline)
+    dc = DistributedCommitter.auto(be, n, B, C5) if args.auto else DistributedCommitter(be, n, B, C5, fused=bool(args.fused), pipeline=args.pipeline)
     full_cols = bench.synth_trace_device(torch, dc.col_count, n, 0xC0FFEE05 + (dc.col_start << 32), dev)
     timed(dc, full_cols, f"cfg5 f64 2^{args.cfg5_log_rows} x 256 Blake3_256, column-sharded", n, C5, 8)
 dist.barrier()

@@ -198,6 +198,25 @@ class DistributedCommitter:
         assert all(c > 0 for _, c in self.shards), "more ranks than columns"
         self.col_start, self.col_count = self.shards[self.rank]
 
+    @classmethod
+    def auto(cls, backend, n_rows, blowup, total_cols, group=None):
+        """Picks the form of the exchange from the shard shape, following the 2-GPU measurements in DESIGN.md: narrow
+        shards (a StarkPack trace per GPU: <= 16 columns per rank) finish their LDE pass in a few milliseconds, where
+        the fused P2P stores save the whole all-to-all; wide shards (>= 64 columns) would make that pass NVLink-bound
+        at 32-byte stores, so they pipeline NCCL all-to-alls of column chunks under the LDE instead. A backend without
+        peer memory (the CPU checker of the tests) gets the plain all-to-all."""
+        world = dist.get_world_size(group)
+        per_rank = (total_cols + world - 1) // world
+        can_fuse = hasattr(backend, "peer_alloc") and world <= 8
+        if world > 1 and per_rank <= 16 and can_fuse:
+            return cls(backend, n_rows, blowup, total_cols, group, fused=True)
+        if world > 1 and per_rank >= 64 and hasattr(backend, "lde"):
+            k = 4
+            while world * k > 16 and k > 1:  # the leaf kernel concatenates at most 16 matrices
+                k //= 2
+            return cls(backend, n_rows, blowup, total_cols, group, pipeline=k if k > 1 else 0)
+        return cls(backend, n_rows, blowup, total_cols, group)
+
     def commit(self, local_cols):
         """local_cols: [col_count, n, w] — this rank's block of the global column list. Returns the 32-byte root
         (identical on every rank); keeps polys / lde shard / leaves / local nodes / top nodes as attributes."""

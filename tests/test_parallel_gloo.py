@@ -65,7 +65,10 @@ def _worker(rank, world, port, field, hash_id, n, blowup, total_cols, seed, q, p
 
         full = fx.synth_f64(seed, total_cols, n) if field == 0 else fx.synth_f128(seed, total_cols, n)
         be = OracleBackend(field, hash_id)
-        dc = DistributedCommitter(be, n, blowup, total_cols, pipeline=pipeline)
+        dc = (DistributedCommitter.auto(be, n, blowup, total_cols) if pipeline < 0
+              else DistributedCommitter(be, n, blowup, total_cols, pipeline=pipeline))
+        if pipeline < 0:
+            assert not dc.fused and dc.pipeline == (4 if total_cols // world >= 64 else 0)
         local = be._t(full[dc.col_start: dc.col_start + dc.col_count])
         root = dc.commit(local)
         nodes = dc.gather_nodes().numpy()
@@ -93,6 +96,8 @@ def _free_port():
     (2, 0, 0, 16, 8, 37, 2),    # pipelined exchange: chunks 16+3 / 16+2
     (2, 0, 0, 16, 4, 21, 4),    # 11 -> chunks 8+3+0+0, 10 -> 8+2+0+0 (empty chunks skipped on every rank)
     (4, 1, 0, 16, 8, 6, 2),     # f128, single-column shards: second chunk empty everywhere
+    (2, 0, 0, 16, 2, 130, -1),  # DistributedCommitter.auto: 65 columns per rank -> 4 chunks; no peer memory on CPU
+    (2, 0, 0, 16, 8, 10, -1),   # auto on a narrow shard without peer memory: plain all-to-all
 ])
 def test_distributed_commit_matches_single_process(oracle, world, field, hash_id, n, blowup, total_cols, pipeline):
     ctx = mp.get_context("spawn")
