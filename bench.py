@@ -2,15 +2,22 @@
 """bench.py — trace LDE + Merkle commit (BASELINE.json metric) on N B200s of one node.
 
 One "step" = one full Prover::build_trace_commitment pass (interpolate columns -> coset LDE -> hash LDE rows ->
-Merkle tree) over one synthetic trace. N=1 workload = BASELINE.json configs[1]: 2^22 rows x 100 Goldilocks
-columns, blowup 8, Blake3_256. N>1: every rank commits its own trace of that shape (independent traces, no
-data-path collective; "weak" scaling) — the StarkPack "one trace per GPU" partition of configs[3].
+Merkle tree) over ONE synthetic trace = BASELINE.json configs[1]: 2^22 rows x 100 Goldilocks columns, blowup 8,
+Blake3_256.
 
-  value        device-resident: trace already in HBM, results left in HBM, CUDA events around K steps
-  e2e          the same work through the C-ABI host entry point wg_commit_trace with pinned host buffers:
-               H2D of the trace and D2H of polys + LDE + leaves + nodes inside the timed region
+  N = 1   value  device-resident: trace already in HBM, results left in HBM, CUDA events around K steps
+  N > 1   value  the SAME trace (same seed on every rank), its columns cut into N contiguous blocks, committed through
+                 the C ABI's wg_sharded_commit_dev: per-rank interpolation + LDE, the column-shard -> row-block exchange
+                 over NVLink (NCCL all-to-all pipelined under the LDE, or P2P stores fused into the LDE's last pass), row
+                 hashing, the subtree, the root all-gather and the top levels. "strong" scaling: value = ms per commit,
+                 CUDA events, max over ranks. The root is asserted equal to the 1-GPU root on every N.
+  e2e          the same work through the C-ABI host entry point with pinned host buffers: H2D of the trace and D2H of
+               polys + LDE + leaves + nodes inside the timed region (N > 1: each rank moves its column block in and its
+               row block out)
   roofline     dominant kernel (LDE contiguous pass): SURVEY 8(d) algorithmic bytes it moves / its CUDA-event time
-  cpu_baseline the CPU oracle (C + OpenMP restatement of the reference, kind "port") on a bounded sample
+  cpu_baseline the CPU oracle (C + OpenMP restatement of the reference's `concurrent` path, kind "port") on a bounded sample
+  replicas     (N > 1) the old figure: one independent trace per GPU, no exchange
+  configs      cfg4 (8 fib traces, one tree) and, where it fits, cfg5 (2^24 x 256) through the same sharded entry point
   --impl reference : that oracle as the reference arm, on the host cores.
 """
 import argparse
@@ -26,7 +33,17 @@ sys.path.insert(0, ROOT)
 
 LOG_ROWS, COLS, BLOWUP = 22, 100, 8
 SEED = 0xC0FFEE02
+SEED5 = 0xC0FFEE05
 METRIC = "lde_merkle_commit_ms_2^22x100_f64_blowup8"
+
+
+def golden_roots():
+    """full-size roots from the CPU oracle (tests/golden/make_full_roots.py); {} if the file is absent"""
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "full_roots.json")) as f:
+            return {k: v["root"] for k, v in json.load(f).items()}
+    except Exception:
+        return {}
 
 
 def algorithmic_bytes(n, cols, blowup, esize=8):
@@ -77,9 +94,9 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def synth_trace_device(torch, cols, n, seed, device):
+def synth_trace_device(torch, cols, n, seed, device, col_start=0):
     """SURVEY 8(d) generator x(c, r) = splitmix64(seed + c*2^32 + r) reduced below p, computed on the GPU with
-    int64 wraparound arithmetic (identical words to tests/fixtures.synth_f64)."""
+    int64 wraparound arithmetic (identical words to tests/fixtures.synth_f64); columns col_start .. col_start+cols."""
     def lsr(x, k):
         return (x >> k) & ((1 << (64 - k)) - 1)
 
@@ -90,7 +107,7 @@ def synth_trace_device(torch, cols, n, seed, device):
     out = torch.empty((cols, n, 1), dtype=torch.int64, device=device)
     r = torch.arange(n, dtype=torch.int64, device=device)
     for c in range(cols):
-        z = r + i64(seed + (c << 32)) + i64(0x9E3779B97F4A7C15)
+        z = r + i64(seed + ((c + col_start) << 32)) + i64(0x9E3779B97F4A7C15)
         z = (z ^ lsr(z, 30)) * i64(0xBF58476D1CE4E5B9)
         z = (z ^ lsr(z, 27)) * i64(0x94D049BB133111EB)
         z = z ^ lsr(z, 31)
@@ -100,82 +117,114 @@ def synth_trace_device(torch, cols, n, seed, device):
     return out
 
 
-def cpu_commit_sample(log_rows_sample, steps=1, warmup=0):
-    """Times the CPU oracle (oracle/oracle.c, C + OpenMP restatement of the reference's concurrent path, kind
-    "port": no Rust toolchain here, so oracle/_ref does not exist) on a 2^log_rows_sample x 100 sample of the
-    workload with every host thread, and scales linearly in rows to the full 2^22 configuration."""
-    import numpy as np
+# ---------------------------------------------------------------------------------------------------------- CPU arm
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
 
+
+def pick_cpu_log_rows(requested):
+    """Full 2^22 rows when the host can do it in bounded time (>= 24 threads, >= 96 GB free: ~45 GB working set),
+    otherwise a 2^20-row sample scaled linearly in rows."""
+    if requested:
+        return requested
+    try:
+        import psutil
+
+        free = psutil.virtual_memory().available
+    except Exception:
+        free = 0
+    return LOG_ROWS if (host_threads() >= 24 and free > 96e9) else 20
+
+
+def cpu_commit_sample(log_rows_sample, runs=1):
+    """Times the CPU oracle (oracle/oracle.c: C + OpenMP restatement of the reference's `concurrent` rayon path — nested
+    parallel coset / row FFTs, concurrent permute, batched transpose, parallel leaf hashing and Merkle levels; kind "port":
+    no Rust toolchain here, so oracle/_ref does not exist) with every host thread. torchrun exports OMP_NUM_THREADS=1, so
+    the thread count is set explicitly."""
     import oracle
     from tests import fixtures as fx
 
     oracle.build()
+    threads = host_threads()
+    oracle.lib().or_set_threads(threads)
     n = 1 << log_rows_sample
     tr = fx.synth_f64(SEED, COLS, n)
-    best = []
-    root = None
-    for i in range(warmup + steps):
+    times, root = [], None
+    for _ in range(max(1, runs)):
         t0 = time.perf_counter()
         r = oracle.commit_trace(0, 0, [tr], BLOWUP, want=("nodes",))
-        dt = time.perf_counter() - t0
+        times.append(time.perf_counter() - t0)
         root = bytes(r["root"])
-        if i >= warmup:
-            best.append(dt)
-    ms_sample = 1e3 * sum(best) / len(best)
+    ms_sample = 1e3 * min(times)
     scale = (1 << LOG_ROWS) / n
+    what = "the full workload" if scale == 1 else f"scaled x{scale:g} (linear in rows) to 2^{LOG_ROWS}"
     return {"value": ms_sample * scale, "unit": "ms", "cores": int(oracle.lib().or_threads()), "kind": "port",
-            "sample": f"2^{log_rows_sample} rows x {COLS} cols f64 blowup {BLOWUP} Blake3_256, {ms_sample:.1f} ms measured, "
-                      f"scaled x{scale:g} (linear in rows) to 2^{LOG_ROWS}",
-            "sample_ms": ms_sample, "sample_root": root.hex()}
+            "sample": f"2^{log_rows_sample} rows x {COLS} cols f64 blowup {BLOWUP} Blake3_256, {ms_sample:.1f} ms measured "
+                      f"(best of {len(times)}), {what}",
+            "sample_ms": ms_sample, "sample_root": root.hex(), "runs": len(times), "host_threads": threads}
 
 
-def workload_config():
-    """`config` of the JSON line, identical in both arms."""
-    return {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit, one trace per GPU",
+def workload_config(world):
+    part = "one GPU" if world == 1 else (f"columns sharded over {world} GPUs (wg_sharded_commit_dev: LDE per column block, row-block "
+                                         "exchange over NVLink, row hashing + subtree per GPU, top levels)")
+    return {"workload": f"2^{LOG_ROWS} rows x {COLS} cols f64 (Goldilocks), blowup {BLOWUP}, Blake3_256 commit of ONE trace, {part}",
             "l2": "inputs (3.4 GB trace, 27 GB LDE) far exceed the 126 MB L2; no flush needed",
-            "value_is": "ms per committed trace = ms_per_step / n_gpus"}
+            "value_is": "ms per commit of the one trace (max over ranks)"}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb = cpu_commit_sample(args.cpu_log_rows, steps=max(1, args.steps), warmup=min(args.warmup, 1))
-    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "ms", "n_gpus": args.gpus,
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    log_rows = pick_cpu_log_rows(args.cpu_log_rows)
+    runs = 1 if log_rows >= 22 else min(3, max(1, args.steps))  # bounded: the sample is never repeated `steps` times
+    cb = cpu_commit_sample(log_rows, runs=runs)
+    gold = golden_roots().get("cfg2")
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": "ms", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["sample_ms"], "higher_is_better": False,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": workload_config(),
-            "reference_arm": "CPU oracle port of the reference's concurrent path on the host cores (Rust toolchain absent); one "
-                             "trace, bounded sample scaled linearly in rows",
+            "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": workload_config(world),
+            "reference_arm": "CPU oracle port of the reference's concurrent path on the host cores (Rust toolchain absent: no "
+                             f"oracle/_ref); {cb['cores']} OpenMP threads; the sample is run {cb['runs']}x whatever --steps says",
             "cpu_baseline": cb,
+            "root_matches_golden": (cb["sample_root"] == gold) if (gold and log_rows == LOG_ROWS) else None,
             "e2e": {"value": cb["value"], "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
-def run_e2e(torch, w, dev, rank, world, steps, warmup, dist):
-    """wg_commit_trace through host buffers: pinned trace in, pinned polys + LDE + leaves + nodes out."""
-    import ctypes as C
+# ---------------------------------------------------------------------------------------------------------- e2e legs
+def _max_over_ranks(torch, dist, dev, ms):
+    if dist is None:
+        return ms
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
 
-    import psutil
+
+def run_e2e(torch, w, dev, steps, warmup):
+    """N = 1: wg_commit_trace through host buffers: pinned trace in, pinned polys + LDE + leaves + nodes out."""
+    import ctypes as C
 
     from starkpack_winterfell_b200._lib import check, lib
 
     n, L = 1 << LOG_ROWS, (1 << LOG_ROWS) * BLOWUP
     rw = (COLS + 7) // 8 * 8
-    need = (2 * n * COLS * 8 + L * rw * 8 + 2 * L * 32) * 1.15
-    with_lde = psutil.virtual_memory().available / max(world, 1) > need
     pin = dict(dtype=torch.int64, pin_memory=True)
     cols_h = torch.empty((COLS, n), **pin)
-    cols_h.copy_(synth_trace_device(torch, COLS, n, SEED + rank, dev)[:, :, 0])
+    cols_h.copy_(synth_trace_device(torch, COLS, n, SEED, dev)[:, :, 0])
     polys_h = torch.empty((COLS, n), **pin)
-    lde_h = torch.empty((L, rw), **pin) if with_lde else None
+    lde_h = torch.empty((L, rw), **pin)
     leaves_h = torch.empty((L, 32), dtype=torch.uint8, pin_memory=True)
     nodes_h = torch.empty((L, 32), dtype=torch.uint8, pin_memory=True)
     root_h = torch.zeros(32, dtype=torch.uint8, pin_memory=True)
     torch.cuda.synchronize()
     colp = (C.c_void_p * COLS)(*[cols_h[c].data_ptr() for c in range(COLS)])
     polp = (C.c_void_p * COLS)(*[polys_h[c].data_ptr() for c in range(COLS)])
-    ldep = (C.c_void_p * 1)(lde_h.data_ptr()) if with_lde else None
+    ldep = (C.c_void_p * 1)(lde_h.data_ptr())
     cpt = (C.c_uint32 * 1)(COLS)
 
     def step():
@@ -184,29 +233,22 @@ def run_e2e(torch, w, dev, rank, world, steps, warmup, dist):
 
     for _ in range(warmup):
         step()
-    if dist is not None:
-        dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
         step()  # synchronous: returns after the D2H copies have landed
     torch.cuda.synchronize()
     ms = 1e3 * (time.perf_counter() - t0) / steps
-    if dist is not None:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
     h2d = n * COLS * 8
-    d2h = n * COLS * 8 + (L * rw * 8 if with_lde else 0) + 2 * L * 32 + 32
-    return {"value": ms / world, "unit": "ms", "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": h2d,
-            "d2h_bytes_per_step": d2h, "root": bytes(root_h.numpy()).hex(),
-            "outputs": "polys + LDE + leaves + nodes + root" if with_lde else "polys + leaves + nodes + root (LDE left on "
-            "device: host RAM too small for N pinned LDE buffers)", "timer": "host perf_counter around synchronous C-ABI calls"}
+    d2h = n * COLS * 8 + L * rw * 8 + 2 * L * 32 + 32
+    return {"value": ms, "unit": "ms", "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h, "root": bytes(root_h.numpy()).hex(), "outputs": "polys + LDE + leaves + nodes + root",
+            "timer": "host perf_counter around synchronous C-ABI calls (wg_commit_trace)"}
 
 
-def run_e2e_resident(torch, w, dev, rank, world, steps, warmup, dist):
-    """Same commit through the resident C-ABI entry (wg_commitment_from_trace): pinned trace in, pinned polys + root out,
-    then TraceCommitment::query for 32 positions (rows + batch Merkle proof); LDE and tree stay in HBM."""
+def run_e2e_resident(torch, w, dev, steps, warmup):
+    """N = 1: the resident C-ABI entry (wg_commitment_from_trace): pinned trace in, pinned polys + root out, then
+    TraceCommitment::query for 32 positions (rows + batch Merkle proof); LDE and tree stay in HBM."""
     import numpy as np
 
     from starkpack_winterfell_b200.matrix import ColMatrix, StarkDomain
@@ -214,7 +256,7 @@ def run_e2e_resident(torch, w, dev, rank, world, steps, warmup, dist):
 
     n = 1 << LOG_ROWS
     cols_h = torch.empty((COLS, n), dtype=torch.int64, pin_memory=True)
-    cols_h.copy_(synth_trace_device(torch, COLS, n, SEED + rank, dev)[:, :, 0])
+    cols_h.copy_(synth_trace_device(torch, COLS, n, SEED, dev)[:, :, 0])
     torch.cuda.synchronize()
     cols_np = cols_h.numpy().view(np.uint64)
     trace = ColMatrix(w.F64, [cols_np[c] for c in range(COLS)])
@@ -237,24 +279,126 @@ def run_e2e_resident(torch, w, dev, rank, world, steps, warmup, dist):
 
     for _ in range(warmup):
         step()
-    if dist is not None:
-        dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
     torch.cuda.synchronize()
     ms = 1e3 * (time.perf_counter() - t0) / steps
-    if dist is not None:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    return {"value": ms / world, "unit": "ms", "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": n * COLS * 8,
+    return {"value": ms, "unit": "ms", "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": n * COLS * 8,
             "d2h_bytes_per_step": int(d2h), "root": root.hex(),
             "outputs": "polys + root + 32 queried rows with their batch Merkle proof; LDE and tree stay in HBM "
                        "(wg_commitment_from_trace / _rows / _digests / _free)"}
 
 
+def run_e2e_sharded(torch, w, sh, dev, rank, world, steps, warmup, dist):
+    """N > 1: wg_sharded_commit through host buffers. Every rank uploads ITS column block from pinned memory, the library
+    commits, and every rank downloads its polynomials, its row block of the LDE (all columns of rows [rank*L/N, ...)),
+    its leaves and subtree and the top levels: together exactly the outputs of the 1-GPU call, each moved once."""
+    import ctypes as C
+
+    import numpy as np
+
+    from starkpack_winterfell_b200._lib import check, lib
+
+    n = 1 << LOG_ROWS
+    s0, cnt = sh.shard_columns(COLS, world, rank)
+    cols_h = torch.empty((cnt, n), dtype=torch.int64, pin_memory=True)
+    cols_h.copy_(synth_trace_device(torch, cnt, n, SEED, dev, col_start=s0)[:, :, 0])
+    polys_h = torch.empty((cnt, n), dtype=torch.int64, pin_memory=True)
+    torch.cuda.synchronize()
+    cols_np, polys_np = cols_h.numpy().view(np.uint64), polys_h.numpy().view(np.uint64)
+    cols_list, polys_list = [cols_np[c] for c in range(cnt)], [polys_np[c] for c in range(cnt)]
+    bufs = {}
+    root, d2h = None, 0
+
+    def step():
+        nonlocal root, d2h
+        h = sh.commit_host(w.F64, w.BLAKE3_256, n, BLOWUP, COLS, cols_list, polys_out=polys_list)
+        if not bufs:
+            bufs["blocks"] = [torch.empty((h.row_count, rw), dtype=torch.int64, pin_memory=True) if c else None
+                              for c, rw in zip(h.block_cols, h.block_row_widths)]
+            bufs["leaves"] = torch.empty((h.row_count, 32), dtype=torch.uint8, pin_memory=True)
+            bufs["nodes"] = torch.empty((h.row_count, 32), dtype=torch.uint8, pin_memory=True)
+            bufs["top"] = torch.empty((max(world, 2), 32), dtype=torch.uint8, pin_memory=True)
+        ptrs = (C.c_void_p * len(bufs["blocks"]))(*[b.data_ptr() if b is not None else None for b in bufs["blocks"]])
+        check(lib().wg_sharded_download(h._h, ptrs, C.c_void_p(bufs["leaves"].data_ptr()), C.c_void_p(bufs["nodes"].data_ptr()),
+                                        C.c_void_p(bufs["top"].data_ptr())))
+        root = h.root()
+        d2h = cnt * n * 8 + sum(b.numel() * 8 for b in bufs["blocks"] if b is not None) + 2 * h.row_count * 32 + max(world, 2) * 32
+        h.close()
+
+    for _ in range(warmup):
+        step()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = _max_over_ranks(torch, dist, dev, 1e3 * (time.perf_counter() - t0) / steps)
+    tot = torch.tensor([cnt * n * 8, d2h], device=dev, dtype=torch.float64)
+    dist.all_reduce(tot)
+    return {"value": ms, "unit": "ms", "ms_per_step": ms, "steps": steps, "h2d_bytes_per_step": int(tot[0].item()),
+            "d2h_bytes_per_step": int(tot[1].item()), "root": root.hex(),
+            "outputs": "per rank: its polys + its row block of the LDE (all columns) + its leaves + subtree + top levels; bytes summed over ranks",
+            "timer": "host perf_counter around synchronous C-ABI calls (wg_sharded_commit + wg_sharded_download), barrier on both sides, max over ranks"}
+
+
+# ---------------------------------------------------------------------------------------------------------- other configs
+def fib_trace_words(torch, n, start, dev):
+    """prover/src/tests/mod.rs:17-29 recurrence mod q as [2, n, 2] int64 (lo, hi) words; Python ints on the host."""
+    import numpy as np
+
+    q = (1 << 128) - 45 * (1 << 40) + 1
+    a, b = start
+    lo = np.empty((2, n), dtype=np.uint64)
+    hi = np.empty((2, n), dtype=np.uint64)
+    m = (1 << 64) - 1
+    la, ha, lb, hb = [], [], [], []
+    for _ in range(n):
+        la.append(a & m)
+        ha.append(a >> 64)
+        lb.append(b & m)
+        hb.append(b >> 64)
+        a = (a + b) % q
+        b = (a + b) % q
+    lo[0], hi[0], lo[1], hi[1] = la, ha, lb, hb
+    out = np.stack([lo, hi], axis=-1)
+    return torch.from_numpy(out.view(np.int64)).to(dev)
+
+
+def run_config_sharded(torch, w, sh, dist, dev, rank, world, name, field, hash_id, n, total_cols, make_local, reps=3):
+    """One of the other BASELINE.json configs through wg_sharded_commit_dev; CUDA events, max over ranks, best of reps."""
+    s0, cnt = sh.shard_columns(total_cols, world, rank)
+    local = make_local(s0, cnt)
+    torch.cuda.synchronize()
+    best, root, ph, sent, ex, k = None, None, None, 0, None, 0
+    for i in range(reps + 1):
+        if dist is not None:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        h = sh.commit_dev(field, hash_id, n, BLOWUP, total_cols, local)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = _max_over_ranks(torch, dist, dev, e0.elapsed_time(e1))
+        if i > 0 and (best is None or ms < best):
+            best = ms
+            ph, sent = h.phases_ms()
+        root, ex, k = h.root(), h.exchange, h.chunks
+        h.close()
+    del local
+    torch.cuda.empty_cache()
+    esize = 8 if field == w.F64 else 16
+    alg = algorithmic_bytes(n, total_cols, BLOWUP, esize)
+    return {"config": name, "rows": n, "total_cols": total_cols, "n_gpus": world, "ms": best, "exchange": ex, "chunks": k,
+            "phases_ms_rank0": {a: round(b, 3) for a, b in ph.items()}, "bytes_sent_rank0": sent, "root": root.hex(),
+            "algorithmic_bytes": alg, "hbm_gbs_per_gpu": alg / world / (best * 1e-3) / 1e9}
+
+
+# ---------------------------------------------------------------------------------------------------------- our arm
 def run_ours(args):
     import torch
 
@@ -276,92 +420,203 @@ def run_ours(args):
         dist = dist_mod
     import starkpack_winterfell_b200 as w
     from starkpack_winterfell_b200 import _lib
+    from starkpack_winterfell_b200 import sharded as sh
     from starkpack_winterfell_b200.device import TraceCommitter
 
+    sh.dist_init(rank, world, device=local)  # wg_init + (N > 1) the library's own NCCL communicator
+    gold = golden_roots()
     n = 1 << LOG_ROWS
-    tc = TraceCommitter(w.F64, w.BLAKE3_256, n, BLOWUP, [COLS], device=dev)
-    tc.cols.copy_(synth_trace_device(torch, COLS, n, SEED + rank, dev))
+    L = n * BLOWUP
     W, K = max(args.warmup, 3), max(args.steps, 1)
-    for _ in range(W):
-        tc.commit()
-    torch.cuda.synchronize()
-    root_warm = tc.root()
-    _lib.profile_enable(True)
-    _lib.profile_read()
     sampler = ClockSampler(local)
-    if rank == 0:
+    extra = {}
+
+    if world == 1:
+        tc = TraceCommitter(w.F64, w.BLAKE3_256, n, BLOWUP, [COLS], device=dev)
+        tc.cols.copy_(synth_trace_device(torch, COLS, n, SEED, dev))
+        for _ in range(W):
+            tc.commit()
+        torch.cuda.synchronize()
+        root_warm = tc.root()
+        _lib.profile_enable(True)
+        _lib.profile_read()
         sampler.start()
-    launches0 = _lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if dist is not None:
+        launches0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(K):
+            tc.commit()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        launches = _lib.launch_count() - launches0
+        clocks = sampler.stop()
+        phases = {k: (v[0] / K, v[1] // K) for k, v in _lib.profile_read().items()}
+        _lib.profile_enable(False)
+        assert tc.root() == root_warm, "root changed between identical steps"
+        root_hex = tc.root().hex()
+        del tc
+        torch.cuda.empty_cache()
+        _lib.check(_lib.lib().wg_shutdown())
+        e2e = run_e2e(torch, w, dev, steps=min(K, 2), warmup=1)
+        torch.cuda.empty_cache()
+        extra["e2e_resident"] = run_e2e_resident(torch, w, dev, steps=min(K, 2), warmup=1)
+        assert extra["e2e_resident"]["root"] == root_hex == e2e["root"], "resident / host-pointer / device-resident roots differ"
+    else:
+        s0, cnt = sh.shard_columns(COLS, world, rank)
+        local_cols = synth_trace_device(torch, cnt, n, SEED, dev, col_start=s0)
+        root_hex = None
+        for _ in range(W):
+            h = sh.commit_dev(w.F64, w.BLAKE3_256, n, BLOWUP, COLS, local_cols)
+            root_hex = h.root().hex()
+            h.close()
+        torch.cuda.synchronize()
+        _lib.profile_enable(True)
+        _lib.profile_read()
+        if rank == 0:
+            sampler.start()
+        launches0 = _lib.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         dist.barrier()
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(K):
-        tc.commit()
-    e1.record()
-    torch.cuda.synchronize()
-    if dist is not None:
+        torch.cuda.synchronize()
+        e0.record()
+        shard_ph, sent, ex, chunks = {}, 0, None, 0
+        for _ in range(K):
+            h = sh.commit_dev(w.F64, w.BLAKE3_256, n, BLOWUP, COLS, local_cols)
+            ph, sent = h.phases_ms()
+            for a, b in ph.items():
+                shard_ph[a] = shard_ph.get(a, 0.0) + b / K
+            assert h.root().hex() == root_hex, "root changed between identical steps"
+            ex, chunks = h.exchange, h.chunks
+            h.close()
+        e1.record()
+        torch.cuda.synchronize()
         dist.barrier()
-    ms = e0.elapsed_time(e1) / K
-    launches = _lib.launch_count() - launches0
-    clocks = sampler.stop() if rank == 0 else None
-    phases = {k: (v[0] / K, v[1] // K) for k, v in _lib.profile_read().items()}
-    _lib.profile_enable(False)
-    assert tc.root() == root_warm, "root changed between identical steps"
-    if dist is not None:
-        t = torch.tensor([ms], device=dev)
+        ms = _max_over_ranks(torch, dist, dev, e0.elapsed_time(e1) / K)
+        launches = _lib.launch_count() - launches0
+        clocks = sampler.stop() if rank == 0 else None
+        phases = {k: (v[0] / K, v[1] // K) for k, v in _lib.profile_read().items()}
+        _lib.profile_enable(False)
+        # per-phase maxima over ranks name the limiting piece
+        names = list(shard_ph)
+        t = torch.tensor([shard_ph[a] for a in names], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    root_hex = tc.root().hex()
-    del tc
-    torch.cuda.empty_cache()
-    e2e = run_e2e(torch, w, dev, rank, world, steps=min(K, 2), warmup=1, dist=dist)
-    torch.cuda.empty_cache()
-    e2e_res = run_e2e_resident(torch, w, dev, rank, world, steps=min(K, 2), warmup=1, dist=dist)
-    assert e2e_res["root"] == root_hex == e2e["root"], "resident / host-pointer / device-resident roots differ"
+        exposed = shard_ph.get("exchange_exposed", 0.0)
+        extra["sharded"] = {"exchange": ex, "chunks": chunks, "cols_rank0": cnt, "bytes_sent_per_gpu": sent,
+                            "phases_ms_max_over_ranks": {a: round(float(v), 3) for a, v in zip(names, t.tolist())},
+                            "nvlink_gbs_per_gpu_exposed_part_only": (sent / (exposed * 1e-3) / 1e9) if exposed > 0.05 else None}
+        del local_cols
+        torch.cuda.empty_cache()
+        _lib.check(_lib.lib().wg_shutdown())
+        e2e = run_e2e_sharded(torch, w, sh, dev, rank, world, steps=min(K, 2), warmup=1, dist=dist)
+        assert e2e["root"] == root_hex, "host-pointer sharded root differs"
+        torch.cuda.empty_cache()
+        _lib.check(_lib.lib().wg_shutdown())
+        # the old figure: one independent trace per GPU, no exchange (replicas)
+        tc = TraceCommitter(w.F64, w.BLAKE3_256, n, BLOWUP, [COLS], device=dev)
+        tc.cols.copy_(synth_trace_device(torch, COLS, n, SEED, dev))
+        tc.commit()
+        dist.barrier()
+        torch.cuda.synchronize()
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record()
+        for _ in range(2):
+            tc.commit()
+        r1.record()
+        torch.cuda.synchronize()
+        rep_ms = _max_over_ranks(torch, dist, dev, r0.elapsed_time(r1) / 2)
+        extra["replicas"] = {"ms_per_step": rep_ms, "ms_per_trace": rep_ms / world, "traces_per_step": world, "root_rank0": tc.root().hex(),
+                             "note": "N independent 2^22 x 100 commits, no data-path collective (round 1's `value`)"}
+        assert tc.root().hex() == root_hex, "sharded root differs from this GPU's own single-GPU commit of the same trace"
+        del tc
+        torch.cuda.empty_cache()
+        _lib.check(_lib.lib().wg_shutdown())
+
+    if gold.get("cfg2"):
+        assert root_hex == gold["cfg2"], f"root {root_hex} differs from the CPU oracle's full-size root {gold['cfg2']}"
+
+    # ---- the other multi-GPU configs of BASELINE.json through the same entry point
+    configs = []
+    if not args.no_configs:
+        n20 = 1 << 20
+
+        def cfg4_local(s0, cnt):
+            parts = []
+            for t in range(s0 // 2, (s0 + cnt + 1) // 2):
+                tr = fib_trace_words(torch, n20, (t + 1, t + 1), dev)
+                lo, hi = max(s0, 2 * t), min(s0 + cnt, 2 * t + 2)
+                parts.append(tr[lo - 2 * t: hi - 2 * t])
+            return torch.cat(parts).contiguous()
+
+        c4 = run_config_sharded(torch, w, sh, dist, dev, rank, world, "cfg4 starkpack: 8 fib traces f128 2^20 x 2, one tree", w.F128,
+                                w.BLAKE3_256, n20, 16, cfg4_local)
+        c4["matches_oracle_root"] = (c4["root"] == gold["cfg4"]) if gold.get("cfg4") else None
+        configs.append(c4)
+        if world >= 4:
+            n24 = 1 << 24
+            c5 = run_config_sharded(torch, w, sh, dist, dev, rank, world, "cfg5 big: f64 2^24 x 256", w.F64, w.BLAKE3_256, n24, 256,
+                                    lambda s0, cnt: synth_trace_device(torch, cnt, n24, SEED5, dev, col_start=s0), reps=2)
+            c5["checked"] = "root equal across N; sampled LDE / leaf / path properties: tests/run_distributed_gpu.py --cfg5 (record under profiles/)"
+            configs.append(c5)
+        else:
+            configs.append({"config": "cfg5 big: f64 2^24 x 256", "n_gpus": world, "skipped": "needs >= 4 GPUs: at N = 2 the 137 GB row block "
+                            "per GPU does not fit next to the LDE send buffers (DESIGN.md)"})
+        _lib.check(_lib.lib().wg_shutdown())
+
+    sh.dist_shutdown()
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return
     peak, peak_src = peaks()
-    L = n * BLOWUP
-    rw = (COLS + 7) // 8 * 8
     # Dominant kernel: the LDE contiguous pass (ntt_pass_kernel<Gl64,11,1,false>) and the LDE strided pass take within a
     # few percent of each other; the contiguous pass is the one that moves SURVEY 8(d)'s algorithmic bytes (it writes the
     # L x C LDE words, 26.8 of the 35.7 GB), so it is the one quoted. `achieved` counts ONLY those algorithmic bytes;
-    # `kernel_io_*` also counts the kernel's own compulsory read of the B*N*C intermediate; `traffic` is the DRAM bytes
-    # ncu measured for one launch (profiles/r1_traffic.json).
+    # `kernel_io_*` also counts the kernel's own compulsory read of the B*N*C intermediate. N > 1: rank 0's column block.
     dom = "lde_contig"
     dom_by_time = max(phases, key=lambda k: phases[k][0])
-    kbytes = L * COLS * 8
-    kio = L * COLS * 8 + L * rw * 8
-    dom_ms = phases[dom][0] / max(phases[dom][1], 1)
-    achieved = kbytes / (dom_ms * 1e-3) / 1e9
-    traffic = None
+    my_cols = COLS if world == 1 else sh.shard_columns(COLS, world, 0)[1]
+    dom_launches = max(phases[dom][1], 1)
+    dom_ms = phases[dom][0] / dom_launches
+    kbytes_launch = L * my_cols * 8 / dom_launches
+    kio_launch = 2 * kbytes_launch
+    achieved = kbytes_launch / (dom_ms * 1e-3) / 1e9
+    traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-            traffic = json.load(f)["phases"][dom]["dram_bytes"]
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+            tj = json.load(f)
+        if world == 1:
+            traffic = tj["phases"][dom]["dram_bytes"]
+            traffic_src = ("cited constant: ncu dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, captured at "
+                           f"commit {tj.get('commit', '?')} (profiles/r2_traffic.json); not re-measured in this run")
     except Exception:
         pass
     alg = algorithmic_bytes(n, COLS, BLOWUP)
-    cb = cpu_commit_sample(args.cpu_log_rows) if world == 1 else None
+    cb = cpu_commit_sample(pick_cpu_log_rows(args.cpu_log_rows)) if world == 1 else None
+    if cb and "the full workload" in cb["sample"]:
+        cb["root_matches_gpu"] = cb["sample_root"] == root_hex
     line = {
-        "metric": METRIC, "value": ms / world, "unit": "ms", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms,
-        "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": workload_config(),
-        "lde_rows_per_s": world * L / (ms * 1e-3), "trace_rows_per_s": world * n / (ms * 1e-3),
-        "commit_roofline": {"algorithmic_bytes": alg, "achieved_gbs": alg / (ms * 1e-3) / 1e9, "frac": alg / (ms * 1e-3) / 1e9 / peak},
-        "clocks": clocks, "e2e": e2e, "e2e_resident": e2e_res, "gpu_launches": int(launches), "root": root_hex,
+        "metric": METRIC, "value": ms, "unit": "ms", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms,
+        "higher_is_better": False, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": workload_config(world),
+        "lde_rows_per_s": L / (ms * 1e-3), "trace_rows_per_s": n / (ms * 1e-3),
+        "commit_roofline": {"algorithmic_bytes": alg, "achieved_gbs_per_gpu": alg / world / (ms * 1e-3) / 1e9,
+                            "frac_per_gpu": alg / world / (ms * 1e-3) / 1e9 / peak},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "root": root_hex,
+        "root_matches_cpu_oracle_full_size": (root_hex == gold["cfg2"]) if gold.get("cfg2") else None,
         "phases_ms": {k: round(v[0], 3) for k, v in phases.items()},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": kbytes, "kernel_ms": dom_ms,
-                     "kernel_share_of_step": dom_ms / ms, "longest_phase": dom_by_time,
-                     "kernel_io_bytes": kio, "kernel_io_gbs": kio / (dom_ms * 1e-3) / 1e9, "kernel_io_frac": kio / (dom_ms * 1e-3) / 1e9 / peak,
-                     "note": "integer-issue bound (ALU and FMA pipes both ~60% busy, DRAM ~25%), see DESIGN.md; HBM fraction "
-                             "reported as the contract asks"},
-        "cpu_baseline": cb,
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": kbytes_launch,
+                     "kernel_ms": dom_ms, "launches_per_step": dom_launches,
+                     "kernel_share_of_step": phases[dom][0] / ms, "longest_phase": dom_by_time,
+                     "kernel_io_bytes": kio_launch, "kernel_io_gbs": kio_launch / (dom_ms * 1e-3) / 1e9,
+                     "kernel_io_frac": kio_launch / (dom_ms * 1e-3) / 1e9 / peak,
+                     "note": "integer-issue bound (ALU and FMA pipes both ~60% busy, DRAM ~25%), see DESIGN.md and "
+                             "profiles/r2_int_peak.jsonl; HBM fraction reported as the contract asks"},
+        "cpu_baseline": cb, "configs": configs,
     }
+    line.update(extra)
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
@@ -374,7 +629,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-log-rows", type=int, default=20, help="rows (log2) of the CPU baseline sample (2^20: ~10 s)")
+    ap.add_argument("--cpu-log-rows", type=int, default=0, help="rows (log2) of the CPU baseline sample; 0 = 22 when the host has "
+                    ">= 24 threads and >= 96 GB free, else 20")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg4 / cfg5 sub-benchmarks")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

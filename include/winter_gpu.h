@@ -223,6 +223,85 @@ int wg_lde_scatter_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t
                        uint32_t n_owners, void* const* d_row_blocks, uint64_t row_width, void* d_scratch,
                        uint64_t scratch_elems, void* stream);
 
+/* ---- one tree over a column-sharded trace on G GPUs, behind the ABI (SURVEY 8(e), 8(b) last row) ------------------------
+ * The reference's entry is one in-process call, Prover::build_trace_commitment (prover/src/lib.rs:615-626), and a leaf
+ * needs the whole row of every column of every aggregated trace (RowMatrix::commit_to_comb_rows,
+ * prover/src/matrix/row_matrix.rs:204-238). Here the GLOBAL column list (trace 0 column 0 ... trace T-1 last column) is cut
+ * into G contiguous blocks (wg_shard_columns); one process per GPU calls wg_sharded_commit* with ITS block. Inside the
+ * library: interpolate + LDE of the local columns, the one exchange that turns column shards into row blocks (rank g
+ * receives rows [g*L/G, (g+1)*L/G) of every shard), row hashing over all columns, the local subtree, an all-gather of the
+ * G subtree roots and the top log2(G) levels. Every rank returns the same root.
+ *
+ * Communicator: rank 0 calls wg_dist_unique_id and ships the WG_DIST_ID_BYTES to the other ranks over any channel; every
+ * rank then calls wg_dist_init (collective; ncclCommInitRank on the wg_init device). NCCL is loaded at run time
+ * (dlopen "libnccl.so.2"); without it wg_dist_* return WG_ERR_UNSUPPORTED and the single-GPU entry points are unaffected.
+ *
+ * Exchange forms (identical results):
+ *   WG_EXCHANGE_ALLTOALL   LDE, then one grouped ncclSend/ncclRecv all-to-all;
+ *   WG_EXCHANGE_PIPELINED  the shard is LDE'd in `chunks` column chunks (multiples of 8 columns) and chunk k's
+ *                          all-to-all runs on its own stream under chunk k+1's LDE;
+ *   WG_EXCHANGE_FUSED_P2P  the LDE's last pass stores each row straight into its owner's receive buffer through
+ *                          peer-mapped pointers (CUDA IPC, NVLink P2P stores): no send buffer, no all-to-all;
+ *   WG_EXCHANGE_AUTO       fused up to 16 columns per rank (G <= 8), pipelined otherwise (plain when one chunk). */
+#define WG_DIST_ID_BYTES 128
+enum { WG_EXCHANGE_AUTO = 0, WG_EXCHANGE_ALLTOALL = 1, WG_EXCHANGE_PIPELINED = 2, WG_EXCHANGE_FUSED_P2P = 3 };
+#define WG_SHARD_MAX_BLOCKS 64 /* received column blocks (ranks x chunks) the leaf kernel concatenates */
+
+int wg_dist_unique_id(uint8_t* id_out /* WG_DIST_ID_BYTES */);
+int wg_dist_init(int rank, int world, const uint8_t* id);
+int wg_dist_shutdown(void);
+int wg_dist_info(int* rank, int* world); /* world 1 / rank 0 before wg_dist_init */
+
+/* Host-only partition logic (no GPU needed; tests/test_cabi_cpu.py and the gloo tests call these):
+ * wg_shard_columns: block of rank `rank` in a list of total_cols columns (first total%world ranks get one more);
+ * wg_shard_chunks : chunk `idx` of `k` of a block of `cols` columns (multiples of 8 except the last non-empty one);
+ * wg_shard_plan   : resolves WG_EXCHANGE_AUTO / clamps `chunks` (ranks x chunks <= WG_SHARD_MAX_BLOCKS);
+ * wg_shard_node_owner: global heap index i of an L-leaf tree over `world` subtrees -> rank -1 (top levels, index into the
+ *                   G-entry top array) or the owning rank and its local heap index. */
+int wg_shard_columns(uint32_t total_cols, uint32_t world, uint32_t rank, uint32_t* start, uint32_t* count);
+int wg_shard_chunks(uint32_t cols, uint32_t k, uint32_t idx, uint32_t* start, uint32_t* count);
+int wg_shard_plan(uint32_t total_cols, uint32_t world, int exchange, uint32_t chunks, int* exchange_out, uint32_t* chunks_out);
+int wg_shard_node_owner(uint64_t n_leaves, uint32_t world, uint64_t index, int* rank_out, uint64_t* local_index_out);
+
+/* Collective. d_local_cols: this rank's columns, contiguous [count][n_rows] on the device; d_local_polys (same shape) may
+ * be NULL (the handle then owns the coefficients). `chunks` = 0 lets the library choose. root_out: 32 host bytes.
+ * The handle keeps this rank's row block (all columns of rows [rank*L/G, (rank+1)*L/G)), leaves and subtree in HBM. */
+int wg_sharded_commit_dev(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t total_cols, const void* d_local_cols,
+                          void* d_local_polys, int exchange, uint32_t chunks, uint8_t* root_out, void** handle, void* stream);
+/* The same through host buffers: local_column_ptrs / local_polys_out list this rank's columns (separate allocations,
+ * as ColMatrix holds them); polys_out may be NULL. */
+int wg_sharded_commit(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t total_cols,
+                      const void* const* local_column_ptrs, void* const* local_polys_out, int exchange, uint32_t chunks,
+                      uint8_t* root_out, void** handle);
+/* shape of the handle: global LDE rows, first row / number of rows held here, received column blocks (global column
+ * order) with their real columns and stored row widths (arrays of WG_SHARD_MAX_BLOCKS), exchange form and chunks used */
+int wg_sharded_info(const void* handle, uint64_t* lde_rows, uint64_t* row_start, uint64_t* row_count, uint32_t* n_blocks,
+                    uint32_t* block_cols, uint32_t* block_row_widths, int* exchange, uint32_t* chunks);
+/* milliseconds on the commit's stream (CUDA events): 0 interpolate, 1 LDE (exchange of earlier chunks runs underneath),
+ * 2 exchange left exposed after the last LDE kernel, 3 row hashing, 4 subtree, 5 root all-gather + top levels;
+ * bytes_sent = LDE bytes this rank shipped to OTHER ranks */
+int wg_sharded_phase_ms(const void* handle, float* ms_out /* 6 */, uint64_t* bytes_sent);
+/* rows at GLOBAL LDE positions inside [row_start, row_start + row_count): n_pos x total_cols elements (pad columns
+ * dropped: RowMatrix::row of every shard, concatenated in global column order) */
+int wg_sharded_rows(const void* handle, uint32_t n_pos, const uint64_t* positions, void* rows_out);
+/* digests by index: which = 0 local leaves, 1 local subtree nodes (heap layout over row_count leaves), 2 top nodes (heap
+ * layout over the G subtree roots; entry 1 = root) */
+int wg_sharded_digests(const void* handle, int which, uint32_t n, const uint64_t* indexes, uint8_t* out);
+/* Collective: the reference's full arrays on every rank (host): leaves_out L x 32 (tree.leaves) and nodes_out L x 32 in heap
+ * layout (crypto/src/merkle/mod.rs:350-374), ready for MerkleTree::from_raw_parts. Either may be NULL. */
+int wg_sharded_gather(const void* handle, uint8_t* leaves_out, uint8_t* nodes_out);
+/* This rank's part to the host: blocks_out[i] (may be NULL per block) receives received column block i as a row_count x
+ * block_row_widths[i] row-major matrix (the rows of RowMatrix shard i this rank owns); leaves_out / nodes_out row_count x 32
+ * (local subtree, heap layout); top_out world x 32. Any may be NULL. */
+int wg_sharded_download(const void* handle, void* const* blocks_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* top_out);
+int wg_sharded_free(void* handle);
+/* Test / single-GPU boxes: the SAME per-rank code for all `world` ranks on one device, device copies standing in for the
+ * exchange (NCCL cannot put two ranks on one GPU). d_cols holds the whole column list [total_cols][n_rows]. Outputs may be
+ * NULL: root_out 32 bytes, leaves_out / nodes_out L x 32 host bytes (stitched reference layout). */
+int wg_sharded_commit_emulated(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t total_cols, uint32_t world,
+                               const void* d_cols, int exchange, uint32_t chunks, uint8_t* root_out, uint8_t* leaves_out,
+                               uint8_t* nodes_out);
+
 #ifdef __cplusplus
 }
 #endif

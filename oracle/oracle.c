@@ -68,6 +68,14 @@ int or_threads(void) {
   return 1;
 #endif
 }
+/* torchrun exports OMP_NUM_THREADS=1; the timed CPU baseline sets its thread count explicitly */
+void or_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
 
 /* ---- scalar helpers exported for the field tests */
 uint64_t or_f64_new(uint64_t v) { return f64_new(v); }
@@ -260,29 +268,39 @@ int or_evaluate_polys_over(int field, const void* const* polys, uint32_t ncols, 
     if (off == 0) return OR_ERR_ZERO_OFFSET;
     f128_eval_offsets(n, blowup, off, (u128*)offsets);
   }
+  /* Segments one after the other (row_matrix.rs:304-306 is a serial `map`); inside Segment::new_with_buffer the B coset
+   * chunks run in parallel, each copy_polys + concurrent::split_radix_fft whose inner / outer FFTs are parallel again
+   * (segments.rs:125-139, 232-272; nested rayon -> nested OpenMP tasks), then the concurrent permute (:276-298), and
+   * finally the batched transpose of row_matrix.rs:314-359 (here per segment: same bytes moved). */
+  int nthreads = or_threads();
+  size_t batches = 1;
+  while ((int)batches < nthreads) batches *= 2;
+  batches *= 2; /* rayon::current_num_threads().next_power_of_two() * 2 */
+#pragma omp parallel
+#pragma omp single
   for (uint32_t s = 0; s < nseg; s++) {
     uint32_t c0 = s * SEGW, np = ncols - c0 < SEGW ? ncols - c0 : SEGW;
     if (np < SEGW) memset(seg, 0, L * SEGW * es);
-#pragma omp parallel for schedule(dynamic)
+#pragma omp taskloop default(shared) grainsize(1)
     for (uint64_t i = 0; i < blowup; i++) {
       if (field == 0) {
         uint64_t* d = (uint64_t*)seg + i * n * SEGW;
         const uint64_t* o = (const uint64_t*)offsets + i * n;
         for (uint64_t r = 0; r < n; r++)
           for (uint32_t c = 0; c < np; c++) d[r * SEGW + c] = f64_mul(((const uint64_t*)polys[c0 + c])[r], o[r]);
-        f64_fft_in_place(d, n, SEGW, (const uint64_t*)twiddles);
+        f64_split_radix_fft(d, n, SEGW, (const uint64_t*)twiddles);
       } else {
         u128* d = (u128*)seg + i * n * SEGW;
         const u128* o = (const u128*)offsets + i * n;
         for (uint64_t r = 0; r < n; r++)
           for (uint32_t c = 0; c < np; c++) d[r * SEGW + c] = f128_mul(((const u128*)polys[c0 + c])[r], o[r]);
-        f128_fft_in_place(d, n, SEGW, (const u128*)twiddles);
+        f128_split_radix_fft(d, n, SEGW, (const u128*)twiddles);
       }
     }
-    if (field == 0) f64_permute((uint64_t*)seg, L, SEGW);
-    else f128_permute((u128*)seg, L, SEGW);
+    if (field == 0) f64_permute_par((uint64_t*)seg, L, SEGW, batches);
+    else f128_permute_par((u128*)seg, L, SEGW, batches);
     /* transpose step: segment s occupies columns [8s, 8s+8) of every row */
-#pragma omp parallel for schedule(static)
+#pragma omp taskloop default(shared) grainsize(4096)
     for (uint64_t r = 0; r < L; r++)
       memcpy((uint8_t*)out + (r * row_width + c0) * es, (uint8_t*)seg + r * SEGW * es, SEGW * es);
   }

@@ -70,6 +70,69 @@ static inline void NAME(fft_in_place)(FE* values, size_t n, size_t w, const FE* 
   if (n >= 2) NAME(fft_rec)(values, n, w, tw, 1, 1, 0);
 }
 
+/* ---- the reference's `concurrent` transform of a segment (prover/src/matrix/segments.rs:232-345; the [E] twin is
+ * math/src/fft/concurrent.rs:121-210): sqrt(n) decomposition, natural in -> bit-reversed out, i.e. the same output as
+ * fft_in_place. transpose (serial, as in the reference: "TODO: investigate concurrent implementation"), inner FFTs over
+ * the rows in parallel (rayon par_chunks_mut -> OpenMP taskloop; must run inside a parallel region), transpose, twiddle
+ * scaling + outer FFTs over the rows in parallel. */
+static void NAME(transpose_square_stretch)(FE* d, size_t size, size_t stretch, size_t w) {
+  /* segments.rs:308-345: blocks of `stretch` consecutive rows-of-w are the matrix entries */
+  size_t bw = stretch * w;
+  for (size_t row = 0; row < size; row++)
+    for (size_t col = row + 1; col < size; col++) {
+      FE* a = d + (row * size + col) * bw;
+      FE* b = d + (col * size + row) * bw;
+      for (size_t t = 0; t < bw; t++) {
+        FE tmp = a[t];
+        a[t] = b[t];
+        b[t] = tmp;
+      }
+    }
+}
+static void NAME(split_radix_fft)(FE* data, size_t n, size_t w, const FE* tw) {
+  unsigned log_n = (unsigned)__builtin_ctzll((unsigned long long)n);
+  if (n < 1024) { /* MIN_CONCURRENT_SIZE (math/src/fft/mod.rs:34): the serial transform */
+    NAME(fft_in_place)(data, n, w, tw);
+    return;
+  }
+  FE g = tw[n / 4]; /* twiddles[twiddles.len() / 2] = w_n (segments.rs:236) */
+  size_t inner_len = (size_t)1 << (log_n / 2), outer_len = n / inner_len, stretch = outer_len / inner_len;
+  NAME(transpose_square_stretch)(data, inner_len, stretch, w);
+#pragma omp taskloop default(shared) grainsize(4)
+  for (size_t i = 0; i < inner_len; i++) NAME(fft_rec)(data + i * outer_len * w, outer_len, w, tw, stretch, stretch, 0);
+  NAME(transpose_square_stretch)(data, inner_len, stretch, w);
+#pragma omp taskloop default(shared) grainsize(4)
+  for (size_t i = 0; i < inner_len; i++) {
+    FE* row = data + i * outer_len * w;
+    if (i > 0) {
+      FE inner_tw = FEXP(g, NAME(permute_index)(inner_len, i)), outer_tw = inner_tw;
+      for (size_t e = 1; e < outer_len; e++) {
+        for (size_t t = 0; t < w; t++) row[e * w + t] = FMUL(row[e * w + t], outer_tw);
+        outer_tw = FMUL(outer_tw, inner_tw);
+      }
+    }
+    NAME(fft_in_place)(row, outer_len, w, tw);
+  }
+}
+/* concurrent permute (segments.rs:276-298): batches of the index range, swap when j > i. Inside a parallel region. */
+static void NAME(permute_par)(FE* v, size_t n, size_t w, size_t batches) {
+  if (batches < 1 || n < 1024) batches = 1;
+  size_t per = n / batches;
+#pragma omp taskloop default(shared) grainsize(1)
+  for (size_t b = 0; b < batches; b++) {
+    size_t end = b + 1 == batches ? n : (b + 1) * per;
+    for (size_t i = b * per; i < end; i++) {
+      size_t j = NAME(permute_index)(n, i);
+      if (j > i)
+        for (size_t t = 0; t < w; t++) {
+          FE tmp = v[i * w + t];
+          v[i * w + t] = v[j * w + t];
+          v[j * w + t] = tmp;
+        }
+    }
+  }
+}
+
 /* math/src/utils/mod.rs:36-46: [1, b, b^2, ...] */
 static void NAME(power_series)(FE b, size_t n, FE one, FE* out) {
   FE acc = one;

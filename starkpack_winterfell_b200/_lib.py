@@ -26,6 +26,9 @@ SYMBOLS = [
     "wg_interpolate_poly_ext", "wg_interpolate_poly_with_offset_ext", "wg_evaluate_poly_ext", "wg_evaluate_poly_with_offset_ext",
     "wg_interpolate_columns_ext", "wg_evaluate_polys_over_ext", "wg_commit_trace_ext",
     "wg_peer_alloc", "wg_peer_open", "wg_peer_close", "wg_peer_free", "wg_lde_scatter_dev",
+    "wg_dist_unique_id", "wg_dist_init", "wg_dist_shutdown", "wg_dist_info", "wg_shard_columns", "wg_shard_chunks", "wg_shard_plan",
+    "wg_shard_node_owner", "wg_sharded_commit_dev", "wg_sharded_commit", "wg_sharded_info", "wg_sharded_phase_ms", "wg_sharded_rows",
+    "wg_sharded_digests", "wg_sharded_gather", "wg_sharded_download", "wg_sharded_free", "wg_sharded_commit_emulated",
 ]
 
 
@@ -99,6 +102,23 @@ def lib():
         L.wg_peer_close.argtypes = [vp]
         L.wg_peer_free.argtypes = [vp]
         L.wg_lde_scatter_dev.argtypes = [i32, vp, u32, u64, u64, vp, u32, vp, u64, vp, u64, vp]
+        L.wg_dist_unique_id.argtypes = [vp]
+        L.wg_dist_init.argtypes = [i32, i32, vp]
+        L.wg_dist_info.argtypes = [vp, vp]
+        L.wg_shard_columns.argtypes = [u32, u32, u32, vp, vp]
+        L.wg_shard_chunks.argtypes = [u32, u32, u32, vp, vp]
+        L.wg_shard_plan.argtypes = [u32, u32, i32, u32, vp, vp]
+        L.wg_shard_node_owner.argtypes = [u64, u32, u64, vp, vp]
+        L.wg_sharded_commit_dev.argtypes = [i32, i32, u64, u64, u32, vp, vp, i32, u32, vp, vp, vp]
+        L.wg_sharded_commit.argtypes = [i32, i32, u64, u64, u32, vp, vp, i32, u32, vp, vp]
+        L.wg_sharded_info.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp]
+        L.wg_sharded_phase_ms.argtypes = [vp, vp, vp]
+        L.wg_sharded_rows.argtypes = [vp, u32, vp, vp]
+        L.wg_sharded_digests.argtypes = [vp, i32, u32, vp, vp]
+        L.wg_sharded_gather.argtypes = [vp, vp, vp]
+        L.wg_sharded_download.argtypes = [vp, vp, vp, vp, vp]
+        L.wg_sharded_free.argtypes = [vp]
+        L.wg_sharded_commit_emulated.argtypes = [i32, i32, u64, u64, u32, u32, vp, i32, u32, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -111,6 +131,11 @@ def check(rc):
 def init(device=0):
     check(lib().wg_init(device))
 
+
+EXCHANGE_AUTO, EXCHANGE_ALLTOALL, EXCHANGE_PIPELINED, EXCHANGE_FUSED_P2P = 0, 1, 2, 3
+EXCHANGE_NAMES = {0: "auto", 1: "alltoall", 2: "pipelined", 3: "fused_p2p"}
+DIST_ID_BYTES = 128
+SHARD_MAX_BLOCKS = 64
 
 PHASES = ["interp_strided", "interp_contig", "lde_strided", "lde_contig", "hash_rows", "merkle"]
 

@@ -971,6 +971,21 @@ static int arena_reserve(size_t bytes) {
   return WG_OK;
 }
 
+// Error paths of the pipelined host-pointer entry points return early (CUDA_TRY / WG_TRY) while async copies against the
+// caller's host buffers and kernels against the shared arena may still be in flight on the three streams; this guard
+// drains them before g_commit_mu is released, so a failed call can neither scribble on memory the caller frees next
+// nor race the next commit's use of the arena.
+struct StreamDrain {
+  cudaStream_t s[3];
+  ~StreamDrain() {
+    for (cudaStream_t x : s)
+      if (x) cudaStreamSynchronize(x);
+  }
+};
+struct LegacyStreamDrain {
+  ~LegacyStreamDrain() { cudaStreamSynchronize(0); }
+};
+
 // Prover::build_trace_commitment through host buffers. Copies ride a second stream so that the D2H of the
 // polynomials overlaps the LDE kernels, the D2H of each trace's LDE overlaps the next trace's LDE / the row hashing,
 // and only the tree comes back after the last kernel.
@@ -1016,6 +1031,7 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
     ldes[t] = (T*)take(L * rws[t] * sizeof(T));
   }
   cudaStream_t sc = g_s_compute, sx = g_s_copy, sh = g_s_h2d;
+  StreamDrain drain{{sc, sx, sh}};
   // upload in up to H2D_CHUNKS column groups; group i is interpolated while group i+1 is still on the wire
   const uint64_t per = (total_cols + H2D_CHUNKS - 1) / H2D_CHUNKS;
   for (uint64_t c0 = 0, k = 0; c0 < total_cols; c0 += per, k++) {
@@ -1095,6 +1111,7 @@ static int h_commit_trace_ext(int hash, uint32_t deg, uint64_t n, uint64_t blowu
     WG_TRY(ldes[t].alloc(L * rws[t] * sizeof(T)));
     lde_c[t] = ldes[t].p;
   }
+  LegacyStreamDrain drain;
   WG_TRY(upload_columns<T>(column_ptrs, (uint32_t)total, n, deg, cols.as<T>(), polys.as<T>(), 0));
   WG_TRY(interpolate_columns_dev<F>(cols.as<T>(), nb, n, polys.as<T>(), scr.as<T>(), se, 0));
   uint64_t c0 = 0;
@@ -1147,7 +1164,7 @@ static int cached_malloc(void** p, size_t bytes) {
 static void cached_free(void* p, size_t bytes) {
   if (!p) return;
   std::lock_guard<std::mutex> lk(g_cache_mu);
-  if (g_block_cache.size() >= 2 * HASH_MAX_TRACES + 4) {
+  if (g_block_cache.size() >= 40) {
     cudaFree(p);
     return;
   }
@@ -1219,6 +1236,7 @@ static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool
   T* cols = inputs_are_polys ? nullptr : (T*)take(colb * total_cols);
   T* scr = (T*)take(se * sizeof(T) + 16);
   cudaStream_t sc = g_s_compute, sx = g_s_copy, sh = g_s_h2d;
+  StreamDrain drain{{sc, sx, sh}};
   const uint64_t per = (total_cols + H2D_CHUNKS - 1) / H2D_CHUNKS;
   for (uint64_t c0 = 0, k = 0; c0 < total_cols; c0 += per, k++) {
     const uint32_t nc = (uint32_t)((total_cols - c0) < per ? (total_cols - c0) : per);
@@ -1398,6 +1416,8 @@ static int h_fri_apply_drp(const void* transposed, uint64_t rows, uint32_t ff, c
 }
 
 }  // namespace wg
+
+#include "dist.cuh"
 
 // ================================================================================================ extern "C"
 using namespace wg;
@@ -1878,6 +1898,300 @@ int wg_lde_scatter_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t
   WG_FIELD_DISPATCH(field,
                     lde_dev<Gl64>((const uint64_t*)d_polys, n_cols, n, blowup, offset_from_internal<Gl64>(offset_host), nullptr, row_width, (uint64_t*)d_scratch, scratch_elems, s, (uint64_t* const*)d_row_blocks, n_owners),
                     lde_dev<F128>((const u128*)d_polys, n_cols, n, blowup, offset_from_internal<F128>(offset_host), nullptr, row_width, (u128*)d_scratch, scratch_elems, s, (u128* const*)d_row_blocks, n_owners));
+}
+
+// ---- sharded commit (dist.cuh)
+int wg_dist_unique_id(uint8_t* id_out) {
+  if (!id_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(nccl_load());
+  static_assert(sizeof(ncclUniqueId) == WG_DIST_ID_BYTES, "ncclUniqueId size");
+  ncclUniqueId id;
+  NCCL_TRY(g_nccl.GetUniqueId(&id));
+  memcpy(id_out, &id, sizeof id);
+  return WG_OK;
+}
+
+int wg_dist_init(int rank, int world, const uint8_t* id) {
+  if (world < 1 || rank < 0 || rank >= world) return fail(WG_ERR_ARG, "rank %d of %d", rank, world);
+  if (!is_pow2((uint64_t)world)) return fail(WG_ERR_ARG, "number of ranks %d must be a power of two", world);
+  WG_TRY(ensure_device());
+  std::lock_guard<std::mutex> lk(g_dist_mu);
+  if (g_dist.on) return fail(WG_ERR_ARG, "wg_dist_init called twice (rank %d of %d is active)", g_dist.rank, g_dist.world);
+  WG_TRY(dist_streams());
+  if (world > 1) {
+    if (!id) return fail(WG_ERR_ARG, "null NCCL id");
+    WG_TRY(nccl_load());
+    ncclUniqueId nid;
+    memcpy(&nid, id, sizeof nid);
+    NCCL_TRY(g_nccl.CommInitRank(&g_dist.comm, world, nid, rank));
+  }
+  g_dist.rank = rank;
+  g_dist.world = world;
+  g_dist.on = true;
+  return WG_OK;
+}
+
+int wg_dist_shutdown(void) {
+  std::lock_guard<std::mutex> lk(g_dist_mu);
+  if (!g_dist.on) return WG_OK;
+  cudaDeviceSynchronize();
+  if (g_dist.world > 1 && g_dist.comm) {
+    // collective: every rank stops using the peers' buffers before anyone unmaps or frees
+    uint8_t* tok = g_dist.d_small;
+    NCCL_TRY(g_nccl.AllGather(tok + 64 * g_dist.world, tok, 4, ncclUint8, g_dist.comm, g_dist.s_comm));
+    CUDA_TRY(cudaStreamSynchronize(g_dist.s_comm));
+    for (auto& pb : g_dist.peer_bufs)
+      for (int g = 0; g < (int)pb.peers.size(); g++)
+        if (g != g_dist.rank && pb.peers[g]) {
+          cudaIpcCloseMemHandle(pb.peers[g]);
+          pb.peers[g] = nullptr;
+        }
+    NCCL_TRY(g_nccl.AllGather(tok + 64 * g_dist.world, tok, 4, ncclUint8, g_dist.comm, g_dist.s_comm));
+    CUDA_TRY(cudaStreamSynchronize(g_dist.s_comm));
+    for (auto& pb : g_dist.peer_bufs) cudaFree(pb.ptr);
+    g_dist.peer_bufs.clear();
+    g_nccl.CommDestroy(g_dist.comm);
+    g_dist.comm = nullptr;
+  }
+  g_dist.on = false;
+  g_dist.rank = 0;
+  g_dist.world = 1;
+  return WG_OK;
+}
+
+int wg_dist_info(int* rank, int* world) {
+  if (rank) *rank = g_dist.rank;
+  if (world) *world = g_dist.world;
+  return WG_OK;
+}
+
+int wg_shard_columns(uint32_t total_cols, uint32_t world, uint32_t rank, uint32_t* start, uint32_t* count) {
+  if (!start || !count || world == 0 || rank >= world) return fail(WG_ERR_ARG, "bad shard query");
+  shard_columns(total_cols, world, rank, start, count);
+  return WG_OK;
+}
+int wg_shard_chunks(uint32_t cols, uint32_t k, uint32_t idx, uint32_t* start, uint32_t* count) {
+  if (!start || !count || k == 0 || idx >= k) return fail(WG_ERR_ARG, "bad chunk query");
+  shard_chunk(cols, k, idx, start, count);
+  return WG_OK;
+}
+int wg_shard_plan(uint32_t total_cols, uint32_t world, int exchange, uint32_t chunks, int* exchange_out, uint32_t* chunks_out) {
+  if (!exchange_out || !chunks_out || world == 0) return fail(WG_ERR_ARG, "bad plan query");
+  if (exchange < WG_EXCHANGE_AUTO || exchange > WG_EXCHANGE_FUSED_P2P) return fail(WG_ERR_ARG, "unknown exchange form %d", exchange);
+  if (exchange == WG_EXCHANGE_FUSED_P2P && world > (uint32_t)PassArgs<Gl64>::MAX_PEERS)
+    return fail(WG_ERR_UNSUPPORTED, "fused exchange supports at most %d ranks", PassArgs<Gl64>::MAX_PEERS);
+  shard_plan(total_cols, world, exchange, chunks, exchange_out, chunks_out);
+  return WG_OK;
+}
+int wg_shard_node_owner(uint64_t n_leaves, uint32_t world, uint64_t index, int* rank_out, uint64_t* local_index_out) {
+  if (!rank_out || !local_index_out || world == 0 || !is_pow2(world) || !is_pow2(n_leaves) || index >= n_leaves || n_leaves < 2 * (uint64_t)world)
+    return fail(WG_ERR_ARG, "bad node query");
+  shard_node_owner(n_leaves, world, index, rank_out, local_index_out);
+  return WG_OK;
+}
+
+int wg_sharded_commit_dev(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t total_cols, const void* d_local_cols,
+                          void* d_local_polys, int exchange, uint32_t chunks, uint8_t* root_out, void** handle, void* stream) {
+  int ex;
+  uint32_t k;
+  WG_TRY(wg_shard_plan(total_cols, (uint32_t)g_dist.world, exchange, chunks, &ex, &k));
+  return sharded_commit_create(field, hash, n_rows, blowup, total_cols, d_local_cols, d_local_polys, exchange, chunks, root_out, handle,
+                               (cudaStream_t)stream);
+}
+
+int wg_sharded_commit(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t total_cols, const void* const* local_column_ptrs,
+                      void* const* local_polys_out, int exchange, uint32_t chunks, uint8_t* root_out, void** handle) {
+  if (!local_column_ptrs || !handle) return fail(WG_ERR_ARG, "null pointer");
+  *handle = nullptr;
+  WG_TRY(ensure_device());
+  int ex;
+  uint32_t k;
+  WG_TRY(wg_shard_plan(total_cols, (uint32_t)g_dist.world, exchange, chunks, &ex, &k));
+  WG_TRY(shard_check_shape(field, hash, n_rows, blowup, total_cols, (uint32_t)g_dist.world));
+  uint32_t s, c;
+  shard_columns(total_cols, (uint32_t)g_dist.world, (uint32_t)g_dist.rank, &s, &c);
+  const size_t colb = n_rows * (field == WG_FIELD_F64 ? 8 : 16);
+  void *d_cols = nullptr, *d_polys = nullptr;
+  WG_TRY(cached_malloc(&d_cols, colb * c));
+  int rc = cached_malloc(&d_polys, colb * c);
+  if (rc == WG_OK) {
+    LegacyStreamDrain drain;
+    for (uint32_t i = 0; i < c && rc == WG_OK; i++)
+      if (cudaMemcpyAsync((char*)d_cols + i * colb, local_column_ptrs[i], colb, cudaMemcpyHostToDevice, 0) != cudaSuccess)
+        rc = fail(WG_ERR_CUDA, "H2D of column %u", i);
+    if (rc == WG_OK) rc = sharded_commit_create(field, hash, n_rows, blowup, total_cols, d_cols, d_polys, exchange, chunks, root_out, handle, 0);
+    for (uint32_t i = 0; local_polys_out && i < c && rc == WG_OK; i++)
+      if (cudaMemcpyAsync(local_polys_out[i], (char*)d_polys + i * colb, colb, cudaMemcpyDeviceToHost, 0) != cudaSuccess)
+        rc = fail(WG_ERR_CUDA, "D2H of polynomial %u", i);
+  }
+  cached_free(d_cols, colb * c);
+  cached_free(d_polys, colb * c);
+  return rc;
+}
+
+int wg_sharded_info(const void* handle, uint64_t* lde_rows, uint64_t* row_start, uint64_t* row_count, uint32_t* n_blocks,
+                    uint32_t* block_cols, uint32_t* block_row_widths, int* exchange, uint32_t* chunks) {
+  const ShardedCommit* h = (const ShardedCommit*)handle;
+  if (!h) return fail(WG_ERR_ARG, "null handle");
+  if (lde_rows) *lde_rows = h->L;
+  if (row_start) *row_start = h->rows * h->rank;
+  if (row_count) *row_count = h->rows;
+  if (n_blocks) *n_blocks = (uint32_t)h->blocks.size();
+  for (size_t i = 0; i < h->blocks.size(); i++) {
+    if (block_cols) block_cols[i] = h->blocks[i].cols;
+    if (block_row_widths) block_row_widths[i] = (uint32_t)h->blocks[i].rw;
+  }
+  if (exchange) *exchange = h->exchange;
+  if (chunks) *chunks = h->K;
+  return WG_OK;
+}
+
+int wg_sharded_phase_ms(const void* handle, float* ms_out, uint64_t* bytes_sent) {
+  const ShardedCommit* h = (const ShardedCommit*)handle;
+  if (!h) return fail(WG_ERR_ARG, "null handle");
+  for (int i = 0; ms_out && i < 6; i++) ms_out[i] = h->phase_ms[i];
+  if (bytes_sent) *bytes_sent = h->bytes_sent;
+  return WG_OK;
+}
+
+int wg_sharded_rows(const void* handle, uint32_t n_pos, const uint64_t* positions, void* rows_out) {
+  const ShardedCommit* h = (const ShardedCommit*)handle;
+  if (!h || !positions || !rows_out) return fail(WG_ERR_ARG, "null pointer");
+  if (n_pos == 0) return WG_OK;
+  const uint64_t r0 = h->rows * h->rank;
+  for (uint32_t i = 0; i < n_pos; i++)
+    if (positions[i] < r0 || positions[i] >= r0 + h->rows)
+      return fail(WG_ERR_ARG, "position %llu is not in this rank's rows [%llu, %llu)", (unsigned long long)positions[i], (unsigned long long)r0,
+                  (unsigned long long)(r0 + h->rows));
+  WG_TRY(ensure_device());
+  const uint32_t w = h->field == WG_FIELD_F64 ? 1 : 2;
+  std::vector<const uint64_t*> ptrs;
+  std::vector<uint32_t> rww, uoff;
+  uint32_t off = 0;
+  for (const ShardBlock& b : h->blocks) {
+    if (!b.cols) continue;
+    ptrs.push_back((const uint64_t*)h->recv + b.off * w);
+    rww.push_back((uint32_t)b.rw * w);
+    uoff.push_back(off);
+    off += b.cols * w;
+  }
+  uoff.push_back(off);
+  const uint32_t nb = (uint32_t)ptrs.size();
+  DevBuf dp, dr, du, dpos, dout;
+  WG_TRY(dp.alloc(nb * 8));
+  WG_TRY(dr.alloc(nb * 4));
+  WG_TRY(du.alloc((nb + 1) * 4));
+  WG_TRY(dpos.alloc(n_pos * 8));
+  WG_TRY(dout.alloc((size_t)n_pos * off * 8));
+  LegacyStreamDrain drain;
+  CUDA_TRY(cudaMemcpyAsync(dp.p, ptrs.data(), nb * 8, cudaMemcpyHostToDevice, 0));
+  CUDA_TRY(cudaMemcpyAsync(dr.p, rww.data(), nb * 4, cudaMemcpyHostToDevice, 0));
+  CUDA_TRY(cudaMemcpyAsync(du.p, uoff.data(), (nb + 1) * 4, cudaMemcpyHostToDevice, 0));
+  CUDA_TRY(cudaMemcpyAsync(dpos.p, positions, n_pos * 8, cudaMemcpyHostToDevice, 0));
+  shard_gather_rows_kernel<<<cdiv((uint64_t)n_pos * off, 256), 256, 0, 0>>>(dp.as<const uint64_t*>(), dr.as<uint32_t>(), du.as<uint32_t>(), nb, off,
+                                                                          dpos.as<uint64_t>(), n_pos, r0, dout.as<uint64_t>());
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  CUDA_TRY(cudaMemcpyAsync(rows_out, dout.p, (size_t)n_pos * off * 8, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_sharded_digests(const void* handle, int which, uint32_t n, const uint64_t* indexes, uint8_t* out) {
+  const ShardedCommit* h = (const ShardedCommit*)handle;
+  if (!h || !indexes || !out) return fail(WG_ERR_ARG, "null pointer");
+  if (which < 0 || which > 2) return fail(WG_ERR_ARG, "which must be 0 (leaves), 1 (subtree nodes) or 2 (top nodes)");
+  if (n == 0) return WG_OK;
+  const uint64_t lim = which == 2 ? (h->world < 2 ? 2 : h->world) : h->rows;
+  for (uint32_t i = 0; i < n; i++)
+    if (indexes[i] >= lim) return fail(WG_ERR_ARG, "index %llu out of range (%llu digests)", (unsigned long long)indexes[i], (unsigned long long)lim);
+  if (which == 2) {
+    for (uint32_t i = 0; i < n; i++) memcpy(out + (size_t)i * 32, h->top_host.data() + indexes[i] * 32, 32);
+    return WG_OK;
+  }
+  WG_TRY(ensure_device());
+  DevBuf didx, dout;
+  WG_TRY(didx.alloc(n * 8));
+  WG_TRY(dout.alloc((size_t)n * 32));
+  LegacyStreamDrain drain;
+  CUDA_TRY(cudaMemcpyAsync(didx.p, indexes, n * 8, cudaMemcpyHostToDevice, 0));
+  gather_digests_kernel<<<cdiv(2 * (uint64_t)n, 256), 256, 0, 0>>>((const uint4*)(which ? h->nodes : h->leaves), didx.as<uint64_t>(), n, dout.as<uint4>());
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  CUDA_TRY(cudaMemcpyAsync(out, dout.p, (size_t)n * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_sharded_gather(const void* handle, uint8_t* leaves_out, uint8_t* nodes_out) {
+  const ShardedCommit* h = (const ShardedCommit*)handle;
+  if (!h) return fail(WG_ERR_ARG, "null handle");
+  WG_TRY(ensure_device());
+  const uint32_t G = h->world;
+  const size_t blk = (size_t)h->rows * 32;
+  if (G == 1) {
+    if (leaves_out) CUDA_TRY(cudaMemcpy(leaves_out, h->leaves, blk, cudaMemcpyDeviceToHost));
+    if (nodes_out) CUDA_TRY(cudaMemcpy(nodes_out, h->nodes, blk, cudaMemcpyDeviceToHost));
+    return WG_OK;
+  }
+  std::lock_guard<std::mutex> lk(g_dist_mu);
+  void* all = nullptr;
+  WG_TRY(cached_malloc(&all, blk * G));
+  int rc = WG_OK;
+  cudaStream_t sx = g_dist.s_comm;
+  auto gather = [&](const uint8_t* src, uint8_t* host_dst) -> int {
+    NCCL_TRY(g_nccl.AllGather(src, all, blk, ncclUint8, g_dist.comm, sx));
+    CUDA_TRY(cudaMemcpyAsync(host_dst, all, blk * G, cudaMemcpyDeviceToHost, sx));
+    CUDA_TRY(cudaStreamSynchronize(sx));
+    return WG_OK;
+  };
+  if (leaves_out) rc = gather(h->leaves, leaves_out);
+  if (rc == WG_OK && nodes_out) {
+    std::vector<uint8_t> locals(blk * G);
+    rc = gather(h->nodes, locals.data());
+    if (rc == WG_OK) stitch_nodes_host(locals.data(), h->top_host.data(), G, h->rows, nodes_out);
+  }
+  cudaStreamSynchronize(sx);
+  cached_free(all, blk * G);
+  return rc;
+}
+
+int wg_sharded_download(const void* handle, void* const* blocks_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* top_out) {
+  const ShardedCommit* h = (const ShardedCommit*)handle;
+  if (!h) return fail(WG_ERR_ARG, "null handle");
+  WG_TRY(ensure_device());
+  LegacyStreamDrain drain;
+  const size_t es = h->esize();
+  for (size_t i = 0; blocks_out && i < h->blocks.size(); i++)
+    if (blocks_out[i] && h->blocks[i].cols)
+      CUDA_TRY(cudaMemcpyAsync(blocks_out[i], (const char*)h->recv + h->blocks[i].off * es, (size_t)h->rows * h->blocks[i].rw * es,
+                               cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, h->leaves, h->rows * 32, cudaMemcpyDeviceToHost, 0));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, h->nodes, h->rows * 32, cudaMemcpyDeviceToHost, 0));
+  if (top_out) memcpy(top_out, h->top_host.data(), (size_t)(h->world < 2 ? 2 : h->world) * 32);
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+int wg_sharded_free(void* handle) {
+  std::lock_guard<std::mutex> lk(g_dist_mu);
+  delete (ShardedCommit*)handle;
+  return WG_OK;
+}
+
+int wg_sharded_commit_emulated(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t total_cols, uint32_t world, const void* d_cols,
+                               int exchange, uint32_t chunks, uint8_t* root_out, uint8_t* leaves_out, uint8_t* nodes_out) {
+  if (!d_cols) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  if (world == 0) return fail(WG_ERR_ARG, "world must be positive");
+  int ex;
+  uint32_t k;
+  WG_TRY(wg_shard_plan(total_cols, world, exchange, chunks, &ex, &k));
+  WG_TRY(shard_check_shape(field, hash, n_rows, blowup, total_cols, world));
+  std::lock_guard<std::mutex> lk(g_dist_mu);
+  WG_FIELD_DISPATCH(field,
+                    sharded_emulate<Gl64>(hash, n_rows, blowup, total_cols, world, (const uint64_t*)d_cols, exchange, chunks, root_out, leaves_out, nodes_out),
+                    sharded_emulate<F128>(hash, n_rows, blowup, total_cols, world, (const u128*)d_cols, exchange, chunks, root_out, leaves_out, nodes_out));
 }
 
 }  // extern "C"

@@ -19,7 +19,7 @@
 
 namespace wg {
 
-constexpr int HASH_MAX_TRACES = 16;
+constexpr int HASH_MAX_TRACES = 64;  // aggregated traces, or ranks x chunks of a sharded commit (WG_SHARD_MAX_BLOCKS)
 
 struct RowHashArgs {
   const void* lde[HASH_MAX_TRACES];      // row-major matrices

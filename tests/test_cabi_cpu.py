@@ -55,3 +55,35 @@ def test_merkle_argument_errors(wg):
         MerkleTree.new(wg.BLAKE3_256, np.zeros((1, 32), dtype=np.uint8))
     with pytest.raises(MerkleTreeError):  # :121-123
         MerkleTree.new(wg.BLAKE3_256, np.zeros((6, 32), dtype=np.uint8))
+
+
+def test_shard_partition_helpers_host_only():
+    """wg_shard_* are host-only (no GPU): the column partition, the chunking and the node-ownership map the sharded
+    commit uses must agree with the Python mirror the gloo tests exercise (starkpack_winterfell_b200/parallel.py)."""
+    from starkpack_winterfell_b200 import _lib, sharded
+    from starkpack_winterfell_b200.parallel import split_chunks, split_columns
+
+    for total, world in [(100, 1), (100, 2), (100, 4), (100, 8), (256, 8), (16, 8), (21, 4), (9, 8)]:
+        assert [sharded.shard_columns(total, world, r) for r in range(world)] == split_columns(total, world)
+    for cols, k in [(50, 2), (13, 2), (128, 4), (25, 4), (8, 1), (7, 3), (100, 8)]:
+        got = sharded.shard_chunks(cols, k)
+        assert got == split_chunks(cols, k)
+        assert sum(c for _, c in got) == cols and all(c % 8 == 0 for _, c in got[:-1] if c and got[-1][1])
+    # auto plan: fused for narrow shards on <= 8 ranks, pipelined otherwise, never more than 64 received blocks
+    assert sharded.shard_plan(16, 8) == (_lib.EXCHANGE_FUSED_P2P, 1)
+    assert sharded.shard_plan(100, 2) == (_lib.EXCHANGE_PIPELINED, 2)
+    assert sharded.shard_plan(256, 8) == (_lib.EXCHANGE_PIPELINED, 2)
+    assert sharded.shard_plan(100, 1) == (_lib.EXCHANGE_ALLTOALL, 1)
+    ex, k = sharded.shard_plan(4096, 32, _lib.EXCHANGE_PIPELINED, 8)
+    assert 32 * k <= _lib.SHARD_MAX_BLOCKS
+    # node ownership reproduces the stitching of the heap layout (crypto/src/merkle/mod.rs:350-374)
+    L, G = 64, 4
+    rows = L // G
+    for i in range(1, L):
+        r, li = sharded.node_owner(L, G, i)
+        if i < G:
+            assert (r, li) == (-1, i)
+        else:
+            m = 1 << (i.bit_length() - 1)
+            per = m // G
+            assert r == (i - m) // per and li == per + (i - m) % per and 1 <= li < rows

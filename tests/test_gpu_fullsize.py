@@ -81,6 +81,16 @@ def test_config2_full_size_properties():
         assert blake3.blake3(data).digest() == bytes(leaves[k])
         assert _merkle_path_ok(0, nodes, leaves, k, root)
     assert not nodes[0].any() and bytes(nodes[1]) == root
+    # the whole tree against the CPU oracle's full-size run of the same input (tests/golden/make_full_roots.py: 107 s on
+    # 8 host threads): root, and SHA-256 of the leaves and of the heap-layout node array
+    import json
+    import os
+
+    with open(os.path.join(os.path.dirname(__file__), "golden", "full_roots.json")) as f:
+        gold = json.load(f)["cfg2"]
+    assert root.hex() == gold["root"]
+    assert hashlib.sha256(leaves.tobytes()).hexdigest() == gold["leaves_sha256"]
+    assert hashlib.sha256(nodes.tobytes()).hexdigest() == gold["nodes_sha256"]
 
 
 @pytest.mark.parametrize("name,hash_id,traces", [

@@ -106,3 +106,20 @@ def test_aggregated_commit(oracle):
     _check_commit(oracle, 1, 0, traces, 4)
     traces = [[rand_ints(0, 32, 11 * t + c) for c in range(3 + t)] for t in range(2)]
     _check_commit(oracle, 0, 0, traces, 2)
+
+
+@pytest.mark.parametrize("field", [0, 1])
+@pytest.mark.parametrize("log_n", [10, 11])
+def test_concurrent_segment_path_equals_serial_columns(oracle, field, log_n):
+    """The oracle's matrix LDE restates the reference's `concurrent` segment transform (sqrt(n) decomposition with nested
+    parallel row FFTs, prover/src/matrix/segments.rs:232-298) from n = 1024 up; every column of its result must equal the
+    serial fft::evaluate_poly_with_offset of that column (math/src/fft/serial.rs:26-57), for an even and an odd log2 n
+    (square and 1x2-stretched transposes). prover/src/matrix/tests.rs:14-40 checks the same property."""
+    n, blowup, cols = 1 << log_n, 4, 11
+    tr = fx.synth_f64(77 + log_n, cols, n) if field == 0 else fx.synth_f128(77 + log_n, cols, n)
+    r = oracle.commit_trace(field, 0, [tr], blowup, want=("polys", "lde"))
+    off = pyref.ints_to_array(field, [pyref.GENERATOR[field]])[0]
+    for c in (0, 5, 10):
+        want = oracle.evaluate_poly_with_offset(field, r["polys"][0][c], off, blowup)
+        assert np.array_equal(r["lde"][0][:, c], want)
+    assert not r["lde"][0][:, cols:].any()
