@@ -95,6 +95,13 @@ int wg_evaluate_polys_over(int field, const void* const* polys, uint32_t n_cols,
 int wg_hash_rows(int field, int hash, const void* row_major, uint64_t rows, uint64_t row_width, uint64_t elems_per_row,
                  uint8_t* leaves_out);
 
+/* RowMatrix::commit_to_comb_rows leaves (prover/src/matrix/row_matrix.rs:204-238) over n_traces ALREADY-BUILT row-major LDE
+ * matrices in host memory: leaf_k = hash_elements(row_k(t0)[..e0] || row_k(t1)[..e1] || ...), without the per-row Vec the
+ * reference concatenates (:217-231). matrices[t] is rows x row_widths[t]; only elems_per_row[t] elements of each row are
+ * hashed. Feed the result to wg_merkle_new for the tree. */
+int wg_hash_comb_rows(int field, int hash, uint32_t n_traces, const void* const* matrices, const uint64_t* row_widths,
+                      const uint64_t* elems_per_row, uint64_t rows, uint8_t* leaves_out);
+
 /* MerkleTree::new -> build_merkle_nodes (crypto/src/merkle/mod.rs:117-136,350-374): nodes_out has n_leaves
  * digests in heap layout (nodes[0] = 0, root = nodes[1]); adopt with MerkleTree::from_raw_parts (:149-161). */
 int wg_merkle_new(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t* nodes_out);
@@ -107,6 +114,11 @@ int wg_merkle_new(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t* n
 int wg_commit_trace(int field, int hash, uint64_t n_rows, uint64_t blowup, uint32_t n_traces,
                     const uint32_t* cols_per_trace, const void* const* column_ptrs, void* const* polys_out,
                     void* const* lde_out, uint8_t* leaves_out, uint8_t* nodes_out, uint8_t* root_out);
+
+/* ColMatrix::evaluate_columns_at (prover/src/matrix/col_matrix.rs:210-216 -> polynom::eval, Horner) for a base-field point:
+ * out[c] = sum_i polys[c][i] * x^i. This is what TracePolyTable::evaluate_at / get_ood_frame call
+ * (prover/src/trace/poly_table.rs:66-80) when E = B. x points at one element in internal representation. */
+int wg_evaluate_columns_at(int field, const void* const* polys, uint32_t n_cols, uint64_t n, const void* x, void* out);
 
 /* Prover::build_constraint_commitment (prover/src/lib.rs:680-715) = RowMatrix::evaluate_polys_over::<8>(composition_poly
  * columns, domain) + commit_to_rows: n_cols coefficient columns of n_coeffs elements each (an extension-field composition

@@ -188,6 +188,15 @@ struct Tables {
     const int lb = log_n <= MAX_LOG_S ? log_n : (log_n + 1) / 2;
     const size_t nlo = (size_t)1 << lb, nhi = (size_t)1 << (log_n - lb);
     if (it == pm.end()) {
+      // keyed by the caller's offset: a caller that walks through many offsets must not grow device memory for ever
+      if (pm.size() >= 32) {
+        cudaDeviceSynchronize();  // kernels that still read the old tables
+        for (auto& kv : pm) {
+          cudaFree(kv.second.lo);
+          cudaFree(kv.second.hi);
+        }
+        pm.clear();
+      }
       Two t;
       t.lb = lb;
       const size_t B = (size_t)1 << log_b;
@@ -223,10 +232,23 @@ static int launch_pass(int layout, bool inv, int log_s, const PassArgs<F>& a, di
   return WG_OK;
 }
 static inline unsigned cdiv(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
-// tuning knob read from the environment (unset: default)
-static int env_int(const char* name, int dflt) {
-  const char* s = getenv(name);
-  return s && *s ? atoi(s) : dflt;
+// Tuning knobs, read from the environment ONCE (first use), never on the per-call path.
+struct Tunables {
+  int lde_q, walk_a, walk_b, zfast;
+  Tunables() {
+    auto env_int = [](const char* name, int dflt) {
+      const char* s = getenv(name);
+      return s && *s ? atoi(s) : dflt;
+    };
+    lde_q = env_int("WG_LDE_Q", 2);
+    walk_a = env_int("WG_WALK_A", 1);
+    walk_b = env_int("WG_WALK_B", 13);
+    zfast = env_int("WG_ZFAST", 1);
+  }
+};
+static const Tunables& tunables() {
+  static const Tunables t;
+  return t;
 }
 
 // ------------------------------------------------------------------------------------------------ phase timing
@@ -252,15 +274,18 @@ static cudaEvent_t prof_event() {
 struct ProfScope {
   int idx = -1;
   cudaStream_t s;
+  cudaEvent_t end = nullptr;
   ProfScope(int phase, cudaStream_t stream) : s(stream) {
     if (!g_prof_on) return;
+    std::lock_guard<std::mutex> lk(g_mu);  // g_prof / g_prof_pool are shared with wg_profile_read and other callers
     ProfRec r{phase, prof_event(), prof_event()};
     cudaEventRecord(r.a, s);
     g_prof.push_back(r);
     idx = (int)g_prof.size() - 1;
+    end = r.b;
   }
   ~ProfScope() {
-    if (idx >= 0) cudaEventRecord(g_prof[idx].b, s);
+    if (idx >= 0) cudaEventRecord(end, s);
   }
 };
 
@@ -281,6 +306,13 @@ static inline void split_passes(int log_n, int* na, int* nb) {
     *nb = log_n - *na;
   }
 }
+
+template <class F>
+static bool elem_is_canonical(const typename F::T& v);
+template <>
+bool elem_is_canonical<Gl64>(const uint64_t& v) { return v < Gl64::P; }
+template <>
+bool elem_is_canonical<F128>(const u128& v) { return u128_lt(v, F128::modulus()); }
 
 template <class F>
 static int check_domain(uint64_t n, uint64_t blowup) {
@@ -391,6 +423,7 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
     if (((uint64_t)1 << sb) < n_peers) return fail(WG_ERR_UNSUPPORTED, "trace too short for %u row blocks", n_peers);
   }
   if (F::is_zero(offset)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
+  if (!elem_is_canonical<F>(offset)) return fail(WG_ERR_ARG, "domain offset is not a reduced field element");
   if (row_width < n_cols) return fail(WG_ERR_ARG, "row_width < n_cols");
   if (n_cols == 0) return WG_OK;
   if (blowup > 65535) return fail(WG_ERR_UNSUPPORTED, "blowup too large");
@@ -452,9 +485,9 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
   // 0: never, 1: only when the table fits at the compiled residency, 2 (default): whenever it fits. At 2^12-point passes
   // (2^23, 2^24 rows) the table leaves room for one block per SM only, and that is still the faster plan: 2^24 x 32
   // columns 175.5 -> 148.2 ms (strided pass 74.2 -> 51.3 ms: one table product per element instead of four).
-  const int q_mode = env_int("WG_LDE_Q", 2);
+  const int q_mode = tunables().lde_q;
   const bool use_q = pm.lb == nb && q_mode && smem_b * (q_mode == 2 ? 1 : FieldCfg<F>::MIN_BLOCKS) <= SMEM_PER_SM;
-  const unsigned walk_a = (unsigned)env_int("WG_WALK_A", 1), walk_b = (unsigned)env_int("WG_WALK_B", 13);
+  const unsigned walk_a = (unsigned)tunables().walk_a, walk_b = (unsigned)tunables().walk_b;
   for (uint64_t c0 = 0; c0 < row_width; c0 += chunk) {
     const uint32_t nc_out = (uint32_t)((row_width - c0) < chunk ? (row_width - c0) : chunk);  // incl. pad columns
     const uint32_t nc_in = c0 >= n_cols ? 0 : (uint32_t)((n_cols - c0) < chunk ? (n_cols - c0) : chunk);
@@ -497,7 +530,7 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
       a.ny = nc_in;
       const unsigned gy = cdiv(nc_in, walk_a ? walk_a : 1);
       ProfScope ps(PH_LDE_A, stream);
-      if (env_int("WG_ZFAST", 1)) {
+      if (tunables().zfast) {
         a.zfast = B;
         WG_TRY(launch_pass<F>(0, false, na, a, dim3(cdiv(N2, tw) * B, gy, 1), stream));
       } else {
@@ -560,7 +593,8 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
   a.one = 1;
   uint64_t off = 0;
   for (uint32_t t = 0; t < n_traces; t++) {
-    if (elems[t] > row_widths[t] || elems[t] == 0) return fail(WG_ERR_ARG, "elems_per_row must be in 1..row_width");
+    // elems == 0 is legal: hash_elements(&[]) is the digest of the empty input (crypto/src/hash/blake/mod.rs:46-59)
+    if (elems[t] > row_widths[t]) return fail(WG_ERR_ARG, "elems_per_row must not exceed row_width");
     a.lde[t] = d_ldes[t];
     a.row_width[t] = (uint32_t)row_widths[t];
     a.unit_off[t] = (uint32_t)off;
@@ -687,6 +721,44 @@ __global__ void field_op_kernel(int op, const typename F::T* a, const typename F
       w = Gl64::as_int(w);
       memcpy(&r, &w, 8);
     }
+  } else if (op >= 96 && op < 104) {
+    // lazily reduced Goldilocks ops (field_lazy.cuh): first operand ANY u64, second <= p; results compared mod p by the test
+    if (F::kFieldId == 0) {
+      uint64_t xa, yb, w = 0;
+      memcpy(&xa, &x, 8);
+      memcpy(&yb, &y, 8);
+      if (op == 96) w = GlLazy::add(xa, yb);
+      else if (op == 97) w = GlLazy::add_b(xa, yb);
+      else if (op == 98) w = GlLazy::sub(xa, yb);
+      else if (op == 99) w = GlLazy::canon(xa);
+      else if (op == 100) w = Gl64::mul(xa, yb);            // lazy first operand through the canonical product
+      else if (op == 101) w = Gl64::mont_shift<28>(xa);
+      else if (op == 102) w = Gl64::mont_shift<52>(xa);
+      else w = GlLazy::mul_w2(xa, yb);
+      memcpy(&r, &w, 8);
+    }
+  } else if (op >= 112 && op < 116) {
+    // 16-point register networks on (x, y, x+1, y+1, ...): 112/113 canonical DIF fwd/inv, 114/115 lazy DIT fwd/inv; output
+    // element (i & 15), canonicalised
+    if (F::kFieldId == 0) {
+      uint64_t xa, yb, v[16];
+      memcpy(&xa, &x, 8);
+      memcpy(&yb, &y, 8);
+#pragma unroll
+      for (int k = 0; k < 16; k++) {
+        const uint64_t t = ((k & 1) ? yb : xa) + (uint64_t)(k >> 1) * 0x9E3779B97F4A7C15ULL;
+        v[k] = t >= Gl64::P ? t - Gl64::P : t;
+      }
+      if (op == 112) radix_ntt<Gl64, 4, false>(v);
+      else if (op == 113) radix_ntt<Gl64, 4, true>(v);
+      else if (op == 114) radix_dit_lazy<4, false>(v);
+      else radix_dit_lazy<4, true>(v);
+      uint64_t w = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++)
+        if ((int)(i & 15) == k) w = GlLazy::canon(v[k]);
+      memcpy(&r, &w, 8);
+    }
   }
   out[i] = r;
 }
@@ -748,6 +820,11 @@ static int commit_trace_dev(int hash, uint64_t n, uint64_t blowup, uint32_t n_tr
   WG_TRY(hash_rows_dev<F>(hash, n_traces, ldes, rws, els, n * blowup, d_leaves, stream));
   return merkle_dev(hash, d_leaves, n * blowup, d_nodes, stream);
 }
+
+// drains the legacy stream on every exit path of a host-pointer entry point (async copies against caller buffers)
+struct LegacyStreamDrainFwd {
+  ~LegacyStreamDrainFwd() { cudaStreamSynchronize(0); }
+};
 
 // RAII device buffer for the host-pointer entry points
 struct DevBuf {
@@ -923,6 +1000,71 @@ static int h_hash_rows(int hash, const void* rows_host, uint64_t rows, uint64_t 
   CUDA_TRY(cudaMemcpyAsync(m.p, rows_host, rows * row_width * sizeof(T), cudaMemcpyHostToDevice, 0));
   const void* ptrs[1] = {m.p};
   WG_TRY(hash_rows_dev<F>(hash, 1, ptrs, &row_width, &elems, rows, l.as<uint8_t>(), 0));
+  CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+// ColMatrix::evaluate_columns_at (col_matrix.rs:210-216): one block per column; thread t evaluates its contiguous slice of
+// coefficients by Horner, then the 256 partial values are combined as a polynomial in x^m (m = slice length).
+template <class F>
+__global__ void __launch_bounds__(256) eval_at_kernel(const typename F::T* polys, uint64_t n, typename F::T x, typename F::T* out) {
+  typedef typename F::T T;
+  __shared__ T part[256];
+  const T* p = polys + (size_t)blockIdx.x * n;
+  const uint64_t m = (n + 255) / 256;
+  const uint64_t lo = (uint64_t)threadIdx.x * m, hi = lo + m < n ? lo + m : n;
+  T acc = F::zero();
+  for (uint64_t i = hi; i > lo; i--) acc = F::add(F::mul(acc, x), p[i - 1]);
+  part[threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    T xm = F::one(), b = x;  // x^m
+    for (uint64_t e = m; e; e >>= 1) {
+      if (e & 1) xm = F::mul(xm, b);
+      b = F::mul(b, b);
+    }
+    T r = F::zero();
+    for (int t = 255; t >= 0; t--) r = F::add(F::mul(r, xm), part[t]);
+    out[blockIdx.x] = r;
+  }
+}
+template <class F>
+static int h_evaluate_columns_at(const void* const* polys, uint32_t n_cols, uint64_t n, const void* x, void* out) {
+  typedef typename F::T T;
+  if (n == 0 || n_cols == 0) return WG_OK;
+  const T xv = offset_from_internal<F>(x);
+  if (!elem_is_canonical<F>(xv)) return fail(WG_ERR_ARG, "evaluation point is not a reduced field element");
+  DevBuf in, res;
+  LegacyStreamDrainFwd drain;
+  WG_TRY(in.alloc((size_t)n_cols * n * sizeof(T)));
+  WG_TRY(res.alloc((size_t)n_cols * sizeof(T)));
+  for (uint32_t c = 0; c < n_cols; c++) CUDA_TRY(cudaMemcpyAsync(in.as<T>() + (size_t)c * n, polys[c], n * sizeof(T), cudaMemcpyHostToDevice, 0));
+  eval_at_kernel<F><<<n_cols, 256, 0, 0>>>(in.as<T>(), n, xv, res.as<T>());
+  CUDA_TRY(cudaGetLastError());
+  g_launches++;
+  CUDA_TRY(cudaMemcpyAsync(out, res.p, (size_t)n_cols * sizeof(T), cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaStreamSynchronize(0));
+  return WG_OK;
+}
+
+template <class F>
+static int h_hash_comb_rows(int hash, uint32_t n_traces, const void* const* mats, const uint64_t* rws, const uint64_t* els, uint64_t rows,
+                            uint8_t* leaves) {
+  typedef typename F::T T;
+  if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
+  std::vector<DevBuf> d(n_traces);
+  DevBuf l;
+  std::vector<const void*> ptrs(n_traces);
+  LegacyStreamDrainFwd drain;
+  WG_TRY(l.alloc(rows * 32));
+  for (uint32_t t = 0; t < n_traces; t++) {
+    if (!mats[t]) return fail(WG_ERR_ARG, "null matrix %u", t);
+    WG_TRY(d[t].alloc(rows * rws[t] * sizeof(T)));
+    CUDA_TRY(cudaMemcpyAsync(d[t].p, mats[t], rows * rws[t] * sizeof(T), cudaMemcpyHostToDevice, 0));
+    ptrs[t] = d[t].p;
+  }
+  WG_TRY(hash_rows_dev<F>(hash, n_traces, ptrs.data(), rws, els, rows, l.as<uint8_t>(), 0));
   CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
@@ -1315,13 +1457,6 @@ __global__ void gather_digests_kernel(const uint4* src, const uint64_t* idx, uin
 static inline bool fri_folding_ok(uint32_t ff) { return ff == 2 || ff == 4 || ff == 8 || ff == 16; }
 
 template <class F>
-static bool elem_is_canonical(const typename F::T& v);
-template <>
-bool elem_is_canonical<Gl64>(const uint64_t& v) { return v < Gl64::P; }
-template <>
-bool elem_is_canonical<F128>(const u128& v) { return u128_lt(v, F128::modulus()); }
-
-template <class F>
 static int fri_commit_layer_dev(int hash, const typename F::T* d_evals, uint64_t n, uint32_t ff, typename F::T* d_transposed,
                                 uint8_t* d_leaves, uint8_t* d_nodes, cudaStream_t stream) {
   typedef typename F::T T;
@@ -1559,6 +1694,20 @@ int wg_hash_rows(int field, int hash, const void* row_major, uint64_t rows, uint
   WG_TRY(ensure_device());
   WG_FIELD_DISPATCH(field, h_hash_rows<Gl64>(hash, row_major, rows, row_width, elems_per_row, leaves_out),
                     h_hash_rows<F128>(hash, row_major, rows, row_width, elems_per_row, leaves_out));
+}
+
+int wg_evaluate_columns_at(int field, const void* const* polys, uint32_t n_cols, uint64_t n, const void* x, void* out) {
+  if (!polys || !x || !out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_evaluate_columns_at<Gl64>(polys, n_cols, n, x, out), h_evaluate_columns_at<F128>(polys, n_cols, n, x, out));
+}
+
+int wg_hash_comb_rows(int field, int hash, uint32_t n_traces, const void* const* matrices, const uint64_t* row_widths,
+                      const uint64_t* elems_per_row, uint64_t rows, uint8_t* leaves_out) {
+  if (!matrices || !row_widths || !elems_per_row || !leaves_out) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  WG_FIELD_DISPATCH(field, h_hash_comb_rows<Gl64>(hash, n_traces, matrices, row_widths, elems_per_row, rows, leaves_out),
+                    h_hash_comb_rows<F128>(hash, n_traces, matrices, row_widths, elems_per_row, rows, leaves_out));
 }
 
 int wg_merkle_new(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t* nodes_out) {

@@ -24,156 +24,54 @@ struct GlLazy {
   typedef uint64_t T;
   static constexpr uint64_t P = Gl64::P;
 
-  // a + b. If the 64-bit sum wraps, the true sum is s + 2^64 = s + eps (mod p); s + eps cannot wrap again because
-  // s = a + b - 2^64 <= a - 2^32 + 1 - ... : with b <= p = 2^64 - eps, s + eps <= a < 2^64.
+  // a + b, a ANY u64, b <= p. If the 64-bit sum wraps, the true sum is s + 2^64 = s + eps (mod p), and s + eps cannot wrap
+  // again: s = a + b - 2^64 <= a - eps, so s + eps <= a. Carry mask on the ALU pipe: 4 ALU + 1 FMA instructions.
   static __device__ __forceinline__ T add(T a, T b) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u32 s0, s1, c;\n\t.reg .u64 s;\n\t"
-        "add.cc.u32 s0, %1, %3;\n\taddc.cc.u32 s1, %2, %4;\n\taddc.u32 c, 0, 0;\n\t"
-        "mov.b64 s, {s0, s1};\n\t"
-        "mad.wide.u32 %0, c, %5, s;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_MONE));
-    return r;
+    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), r0, r1;
+    asm("{\n\t.reg .u32 m;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\taddc.cc.u32 %1, %3, %5;\n\tsubc.u32 m, 0, 0;\n\t"
+        "add.cc.u32 %0, %0, m;\n\t"
+        "madc.lo.u32 %1, %1, %6, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ONE));
+    return ((uint64_t)r1 << 32) | r0;
   }
-  // the same with the carry read on the FMA pipe (IMAD.X) instead of the ALU pipe
+  // the same with the carry word and its mask on the FMA pipe: 3 ALU + 3 FMA
   static __device__ __forceinline__ T add_b(T a, T b) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u32 s0, s1, c;\n\t.reg .u64 s;\n\t"
-        "add.cc.u32 s0, %1, %3;\n\taddc.cc.u32 s1, %2, %4;\n\tmadc.lo.u32 c, %5, %5, 0;\n\t"
-        "mov.b64 s, {s0, s1};\n\t"
-        "mad.wide.u32 %0, c, %6, s;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ZERO), "r"(K_MONE));
-    return r;
+    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), r0, r1;
+    asm("{\n\t.reg .u32 c, m;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\taddc.cc.u32 %1, %3, %5;\n\tmadc.lo.u32 c, %7, %7, 0;\n\t"
+        "mul.lo.u32 m, c, %8;\n\t"
+        "add.cc.u32 %0, %0, m;\n\t"
+        "madc.lo.u32 %1, %1, %6, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ONE), "r"(K_ZERO), "r"(K_MONE));
+    return ((uint64_t)r1 << 32) | r0;
   }
-  // a - b. On a borrow the true difference is d - 2^64 = d - eps (mod p), i.e. d + 0xFFFFFFFF00000001 (mod 2^64); with the
-  // borrow mask m = 0xFFFFFFFF that is d + m*0xFFFFFFFF (= 0xFFFFFFFE00000001) + 2^32. d - eps cannot wrap below zero:
-  // d = a - b + 2^64 >= 2^64 - p = eps for b <= p.
-  static __device__ __forceinline__ T sub(T a, T b) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u32 d0, d1, m;\n\t.reg .u64 d;\n\t"
-        "sub.cc.u32 d0, %1, %3;\n\tsubc.cc.u32 d1, %2, %4;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.u32 d1, d1, m;\n\t"
-        "mov.b64 d, {d0, d1};\n\t"
-        "mad.wide.u32 %0, m, %5, d;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_MONE));
-    return r;
-  }
-  static __device__ __forceinline__ T sub_b(T a, T b) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u32 d0, d1, m;\n\t.reg .u64 d;\n\t"
-        "sub.cc.u32 d0, %1, %3;\n\tsubc.cc.u32 d1, %2, %4;\n\tsubc.u32 m, 0, 0;\n\t"
-        "mad.lo.u32 d1, m, %5, d1;\n\t"
-        "mov.b64 d, {d0, d1};\n\t"
-        "mad.wide.u32 %0, m, %6, d;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_MONE), "r"(K_MONE));
-    return r;
-  }
-  // any u64 -> [0,p): a >= p exactly when a + eps wraps
+  // a - b, a ANY u64, b <= p: Gl64::sub's sequence is already the lazy form (borrow -> + p, which cannot wrap for b <= p)
+  static __device__ __forceinline__ T sub(T a, T b) { return Gl64::sub(a, b); }
+  static __device__ __forceinline__ T sub_b(T a, T b) { return Gl64::sub(a, b); }
+  // any u64 -> [0,p): a >= p exactly when a + eps wraps, and then a - p = a + eps (mod 2^64)
   static __device__ __forceinline__ T canon(T a) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u32 t, c;\n\t"
-        "add.cc.u32 t, %1, 0xFFFFFFFF;\n\taddc.cc.u32 t, %2, 0;\n\taddc.u32 c, 0, 0;\n\t"
-        "mad.wide.u32 %0, c, %4, %3;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "l"(a), "r"(K_MONE));
-    return r;
+    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), r0, r1;
+    asm("{\n\t.reg .u32 t, m;\n\t"
+        "add.cc.u32 t, %2, 0xFFFFFFFF;\n\taddc.cc.u32 t, %3, 0;\n\tsubc.u32 m, 0, 0;\n\t"
+        "add.cc.u32 %0, %2, m;\n\t"
+        "madc.lo.u32 %1, %3, %4, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1)
+        : "r"(a0), "r"(a1), "r"(K_ONE));
+    return ((uint64_t)r1 << 32) | r0;
   }
-
-  // Montgomery product a*w*2^-64 mod p, a ANY u64, w < p; result in [0,p). The 128-bit product is accumulated through
-  // IMAD.WIDE's 64-bit addend (no carry chain: each partial sum provably fits 64 bits), then the reference's reduction
-  // (f64/mod.rs:651-661) regrouped as in Gl64::mont_red; xh <= p - 2 for a < 2^64, so xh + a1 + e < 2^64 still holds.
-  static __device__ __forceinline__ T mul_w(T a, T w) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)w, b1 = (uint32_t)(w >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u64 t, v, x, u, s;\n\t.reg .u32 t0, t1, v0, v1, x0, x1, u0, u1, q, s0, s1, m;\n\t"
-        "mul.wide.u32 t, %1, %3;\n\t"              // a0*b0
-        "mov.b64 {t0, t1}, t;\n\t"
-        "mul.wide.u32 v, %1, %4;\n\t"              // a0*b1
-        "mad.wide.u32 v, t1, 1, v;\n\t"            // + t1            (< 2^64)
-        "mov.b64 {v0, v1}, v;\n\t"
-        "mul.wide.u32 x, %2, %3;\n\t"              // a1*b0
-        "mad.wide.u32 x, v0, 1, x;\n\t"            // + v0            (< 2^64): x0 = limb 1
-        "mov.b64 {x0, x1}, x;\n\t"
-        "mul.wide.u32 u, %2, %4;\n\t"              // a1*b1
-        "mad.wide.u32 u, v1, 1, u;\n\t"
-        "mad.wide.u32 u, x1, 1, u;\n\t"            // (u1:u0) = limbs 3, 2
-        "mov.b64 {u0, u1}, u;\n\t"
-        // reduction: q = (x0 + t0) mod 2^32 with carry e; s = (u1:u0) + q + e - (q:t0); + p on borrow
-        "add.cc.u32 q, x0, t0;\n\t"
-        "addc.cc.u32 s0, u0, q;\n\taddc.u32 s1, u1, 0;\n\t"
-        "sub.cc.u32 s0, s0, t0;\n\tsubc.cc.u32 s1, s1, q;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.u32 s1, s1, m;\n\t"
-        "mov.b64 s, {s0, s1};\n\t"
-        "mad.wide.u32 %0, m, %5, s;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_MONE));
-    return r;
-  }
-  // same product with the two middle accumulations on the ALU pipe (pipe balance)
+  // products and power-of-two shifts accept ANY u64 first operand (x*w < 2^64 * p keeps the Montgomery reduction exact,
+  // its high word xh <= p - 2 so xh + a1 + e cannot overflow) and return canonical values
+  static __device__ __forceinline__ T mul_w(T a, T w) { return Gl64::mul(a, w); }
   static __device__ __forceinline__ T mul_w2(T a, T w) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)w, b1 = (uint32_t)(w >> 32);
-    uint64_t r;
-    asm("{\n\t.reg .u64 t, v, x, u, s;\n\t.reg .u32 t0, t1, v0, v1, x0, x1, u0, u1, l1, h0, h1, q, s0, s1, m;\n\t"
-        "mul.wide.u32 t, %1, %3;\n\tmul.wide.u32 v, %1, %4;\n\tmul.wide.u32 x, %2, %3;\n\tmul.wide.u32 u, %2, %4;\n\t"
-        "mov.b64 {t0, t1}, t;\n\tmov.b64 {v0, v1}, v;\n\tmov.b64 {x0, x1}, x;\n\t"
-        "mad.wide.u32 u, v1, 1, u;\n\t"
-        "mad.wide.u32 u, x1, 1, u;\n\t"
-        "mov.b64 {u0, u1}, u;\n\t"
-        "add.cc.u32 l1, t1, v0;\n\taddc.cc.u32 h0, u0, 0;\n\taddc.u32 h1, u1, 0;\n\t"
-        "add.cc.u32 l1, l1, x0;\n\taddc.cc.u32 h0, h0, 0;\n\taddc.u32 h1, h1, 0;\n\t"
-        "add.cc.u32 q, l1, t0;\n\t"
-        "addc.cc.u32 s0, h0, q;\n\taddc.u32 s1, h1, 0;\n\t"
-        "sub.cc.u32 s0, s0, t0;\n\tsubc.cc.u32 s1, s1, q;\n\tsubc.u32 m, 0, 0;\n\t"
-        "sub.u32 s1, s1, m;\n\t"
-        "mov.b64 s, {s0, s1};\n\t"
-        "mad.wide.u32 %0, m, %5, s;\n\t}"
-        : "=l"(r)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_MONE));
-    return r;
+    // 64x64 product by the compiler (mul.lo.u64 / mul.hi.u64 share their partial products: 4 IMAD.WIDE + carries)
+    const unsigned __int128 x = (unsigned __int128)a * w;
+    return Gl64::mont_red((uint64_t)(x >> 64), (uint64_t)x);
   }
-
-  // Montgomery reduction of x << S (Gl64::mont_shift) for ANY u64 x, canonical result; the final + p on borrow through
-  // IMAD.WIDE as above.
   template <int S>
-  static __device__ __forceinline__ T mont_shift(T x) {
-    static_assert(S > 0 && S < 64, "shift out of range");
-    uint32_t x0 = (uint32_t)x, x1 = (uint32_t)(x >> 32);
-    uint64_t r;
-    if (S < 32) {
-      const uint32_t l0 = x0 << (S & 31), l1 = __funnelshift_l(x0, x1, S & 31), h0 = x1 >> ((32 - S) & 31);
-      asm("{\n\t.reg .u32 q, s0, s1, m;\n\t.reg .u64 s;\n\t"
-          "add.cc.u32 q, %2, %1;\n\t"
-          "addc.cc.u32 s0, %3, q;\n\taddc.u32 s1, 0, 0;\n\t"
-          "sub.cc.u32 s0, s0, %1;\n\tsubc.cc.u32 s1, s1, q;\n\tsubc.u32 m, 0, 0;\n\t"
-          "sub.u32 s1, s1, m;\n\t"
-          "mov.b64 s, {s0, s1};\n\t"
-          "mad.wide.u32 %0, m, %4, s;\n\t}"
-          : "=l"(r)
-          : "r"(l0), "r"(l1), "r"(h0), "r"(K_MONE));
-    } else {
-      constexpr int Q = S - 32;
-      const uint32_t l1 = Q ? x0 << (Q & 31) : x0, h0 = Q ? __funnelshift_l(x0, x1, Q & 31) : x1,
-                     h1 = Q ? x1 >> ((32 - Q) & 31) : 0u;
-      asm("{\n\t.reg .u32 s0, s1, m;\n\t.reg .u64 s;\n\t"
-          "add.cc.u32 s0, %2, %1;\n\taddc.u32 s1, %3, 0;\n\t"
-          "sub.cc.u32 s1, s1, %1;\n\tsubc.u32 m, 0, 0;\n\t"
-          "sub.u32 s1, s1, m;\n\t"
-          "mov.b64 s, {s0, s1};\n\t"
-          "mad.wide.u32 %0, m, %4, s;\n\t}"
-          : "=l"(r)
-          : "r"(l1), "r"(h0), "r"(h1), "r"(K_MONE));
-    }
-    return r;
-  }
+  static __device__ __forceinline__ T mont_shift(T x) { return Gl64::mont_shift<S>(x); }
 
   // |x * w16^(+-idx)| up to the sign Gl64::root16_neg reports (x any u64, result canonical)
   template <bool INV, int IDX>
@@ -181,9 +79,9 @@ struct GlLazy {
     constexpr int e = Gl64::root16_e<INV>(IDX);
     constexpr int sh = (e >= 96 && e < 160) ? e - 96 : e;
     if constexpr (sh > 0 && sh < 64) {
-      return mont_shift<sh>(x);
+      return Gl64::mont_shift<sh>(x);
     } else {
-      return mul_w(x, Gl64::pow2_mod(e));
+      return Gl64::mul(x, Gl64::pow2_mod(e));
     }
   }
 };

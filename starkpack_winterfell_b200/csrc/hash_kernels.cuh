@@ -56,7 +56,9 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const Row
   }
   bool sha_done = false;
 
-  for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done); u0 += SU) {
+  // an empty row still takes one (padding-only) block: the digest of the empty input
+  for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done) || (HASH == HASH_BLAKE3_256 && nbytes == 0 && u0 == 0);
+       u0 += SU) {
     // ---- stage SU units of each of the warp's 32 rows: issue all SU loads first (one long-scoreboard wait per
     // slab instead of one per element), then convert and store
     uint64_t vals[SU];

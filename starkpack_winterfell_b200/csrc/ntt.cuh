@@ -22,6 +22,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "field.cuh"
+#include "field_lazy.cuh"
 
 namespace wg {
 
@@ -106,6 +107,24 @@ __device__ __forceinline__ void radix_ntt(typename F::T (&a)[1 << LR]) {
 #pragma unroll
   for (int i = 0; i < R; i++) a[i] = b[i];
 }
+
+// Which register network a field uses. Goldilocks: the decimation-in-time network on lazily reduced values
+// (field_lazy.cuh; inputs canonical, outputs any u64 congruent mod p, so a pass canonicalises whatever it stores without a
+// multiplication in between). Everything else: the canonical decimation-in-frequency network above.
+template <class F, int LR, bool INV>
+struct RadixNet {
+  static constexpr bool LAZY = false;
+  static __device__ __forceinline__ void run(typename F::T (&a)[1 << LR]) { radix_ntt<F, LR, INV>(a); }
+  static __device__ __forceinline__ typename F::T canon(typename F::T v) { return v; }
+};
+#if defined(WG_DIT_LAZY) && defined(__CUDACC__)
+template <int LR, bool INV>
+struct RadixNet<Gl64, LR, INV> {
+  static constexpr bool LAZY = true;
+  static __device__ __forceinline__ void run(uint64_t (&a)[1 << LR]) { radix_dit_lazy<LR, INV>(a); }
+  static __device__ __forceinline__ uint64_t canon(uint64_t v) { return GlLazy::canon(v); }
+};
+#endif
 
 // ---------------------------------------------------------------------------------------------- compile-time plan
 template <class F>
@@ -280,7 +299,8 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
       for (int r = 0; r < R; r++) a[r] = tile[C::phys(s0 + (r << LOGP), w)];
     }
 
-    if (live) radix_ntt<F, LR, INV>(a);
+    typedef RadixNet<F, LR, INV> Net;
+    if (live) Net::run(a);
 
     if (!LAST) {
       // The block's first step 0 runs while the shared twiddle table is still being filled (its loads overlap the
@@ -293,6 +313,7 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
         for (int j = 0; j < R; j++) {
           T v = a[j];
           if (j > 0) v = F::mul(v, tws[C::tws_off(U) + (j << LOGP) + m_rest]);
+          else if (Net::LAZY) v = Net::canon(v);  // the next step's butterflies want canonical inputs
           tile[C::phys(s0 + (j << LOGP), w)] = v;
         }
       }
@@ -338,6 +359,8 @@ __device__ __forceinline__ void pass_step(const PassArgs<F>& A, typename F::T* t
             v = F::mul(v, table2<F>(A.tm_lo, A.tm_hi, A.tm_lb, e));
           } else if (A.has_const) {
             v = F::mul(v, A.post_const);
+          } else if (Net::LAZY) {
+            v = Net::canon(v);  // results leave the chip canonical, as the reference's are
           }
           const uint32_t jj = (uint32_t)(nat0 + (j << shift_out));
           if (A.n_peers) {

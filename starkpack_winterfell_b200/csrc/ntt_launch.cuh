@@ -1,6 +1,7 @@
 // Launch dispatch for ntt_pass_kernel instantiations. Each field gets its own translation unit
 // (ntt_gl64.cu / ntt_f128.cu) so the two compile in parallel; api.cu only sees the declaration below.
 #pragma once
+#include <atomic>
 #include "ntt.cuh"
 
 namespace wg {
@@ -27,7 +28,7 @@ inline int pass_log_tw(int log_s) {
   template <int LOG_S, int LAYOUT, bool INV>                                                                    \
   static cudaError_t launch_one_##F(const PassArgs<F>& a, dim3 grid, cudaStream_t stream) {                     \
     typedef PassCfg<F, LOG_S, LAYOUT> C;                                                                        \
-    static bool attr_set = false;                                                                               \
+    static std::atomic<bool> attr_set{false};                                                                   \
     constexpr size_t QB = LAYOUT == 1 ? sizeof(F::T) << LOG_S : 0;                                              \
     constexpr size_t MAXB = C::SMEM_BYTES + QB > SMEM_PER_SM ? C::SMEM_BYTES : C::SMEM_BYTES + QB;              \
     if (!attr_set && MAXB > 48 * 1024) {                                                                        \

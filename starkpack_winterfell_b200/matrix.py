@@ -126,3 +126,17 @@ class RowMatrix:
     def commit_to_rows(self, hash_id):
         """RowMatrix::commit_to_rows (row_matrix.rs:183-203)."""
         return MerkleTree.new(hash_id, self.hash_rows(hash_id))
+
+    def commit_to_comb_rows(self, hash_id, traces_lde):
+        """RowMatrix::commit_to_comb_rows (row_matrix.rs:204-238): one tree whose leaf k hashes row k of every matrix in
+        `traces_lde`, concatenated; as in the reference `self` must be traces_lde[0] (it skips index 0, :220)."""
+        assert traces_lde and traces_lde[0] is self, "self must be the first of traces_lde (row_matrix.rs:220)"
+        rows = self.num_rows()
+        assert all(m.num_rows() == rows and m.field == self.field for m in traces_lde)
+        k = len(traces_lde)
+        ptrs = (C.c_void_p * k)(*[m.data.ctypes.data for m in traces_lde])
+        rws = (C.c_uint64 * k)(*[m.row_width for m in traces_lde])
+        els = (C.c_uint64 * k)(*[m.elements_per_row for m in traces_lde])
+        leaves = np.empty((rows, 32), dtype=np.uint8)
+        check(lib().wg_hash_comb_rows(self.field, hash_id, k, ptrs, rws, els, rows, C.c_void_p(leaves.ctypes.data)))
+        return MerkleTree.new(hash_id, leaves)

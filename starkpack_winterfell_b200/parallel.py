@@ -192,6 +192,9 @@ class DistributedCommitter:
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         assert self.world & (self.world - 1) == 0, "number of ranks must be a power of two"
+        # fail before any work: the leaf kernel concatenates at most SHARD_MAX_BLOCKS matrices, the fused LDE has 8 peer slots
+        assert self.world * max(pipeline, 1) <= _lib.SHARD_MAX_BLOCKS, "ranks x pipeline chunks exceeds the leaf kernel's matrix limit"
+        assert not fused or self.world <= 8, "the fused exchange supports at most 8 ranks"
         self.L = n_rows * blowup
         assert self.L % self.world == 0 and self.L // self.world >= 2
         self.shards = split_columns(total_cols, self.world)
@@ -212,7 +215,7 @@ class DistributedCommitter:
             return cls(backend, n_rows, blowup, total_cols, group, fused=True)
         if world > 1 and per_rank >= 64 and hasattr(backend, "lde"):
             k = 4
-            while world * k > 16 and k > 1:  # the leaf kernel concatenates at most 16 matrices
+            while world * k > _lib.SHARD_MAX_BLOCKS and k > 1:  # the leaf kernel's matrix limit
                 k //= 2
             return cls(backend, n_rows, blowup, total_cols, group, pipeline=k if k > 1 else 0)
         return cls(backend, n_rows, blowup, total_cols, group)

@@ -21,6 +21,107 @@ class TraceCommitment:
         return self.main_segment_tree.root()
 
 
+class EvaluationFrame:
+    """air/src/air/mod.rs EvaluationFrame: the current and the next row of the trace at one LDE step."""
+
+    def __init__(self, num_columns, field=F64):
+        shape = (num_columns,) if field == F64 else (num_columns, 2)
+        self.current, self.next = np.zeros(shape, dtype=np.uint64), np.zeros(shape, dtype=np.uint64)
+
+
+class TraceLde:
+    """prover/src/trace/trace_lde.rs:21-108: owns the main-segment LDE (RowMatrix of base elements), the auxiliary
+    segment LDEs and the blowup, and hands evaluation frames to the constraint evaluator. The main segment may also be a
+    ResidentCommitment (the LDE stays in HBM and a frame is two gathered rows, wg_commitment_rows)."""
+
+    def __init__(self, main_trace_lde, blowup, trace_index=0):
+        self.main_segment_lde, self.aux_segment_ldes, self._blowup, self._trace = main_trace_lde, [], blowup, trace_index
+
+    def _resident(self):
+        return isinstance(self.main_segment_lde, ResidentCommitment)
+
+    def add_aux_segment(self, aux_segment_lde):
+        assert self.trace_len() == aux_segment_lde.num_rows(), \
+            "number of rows in auxiliary segment must be of the same as in the main segment"
+        self.aux_segment_ldes.append(aux_segment_lde)
+
+    def main_trace_width(self):
+        return self.main_segment_lde.cols_per_trace[self._trace] if self._resident() else self.main_segment_lde.num_cols()
+
+    def aux_trace_width(self):
+        return sum(m.num_cols() for m in self.aux_segment_ldes)
+
+    def trace_len(self):
+        return self.main_segment_lde.lde_rows if self._resident() else self.main_segment_lde.num_rows()
+
+    def blowup(self):
+        return self._blowup
+
+    def read_main_trace_frame_into(self, lde_step, frame):
+        # at the end of the trace, next state wraps around and we read the first step again (trace_lde.rs:78-90)
+        nxt = (lde_step + self._blowup) % self.trace_len()
+        if self._resident():
+            rows = self.main_segment_lde.rows(self._trace, [lde_step, nxt])
+            frame.current[...] = rows[0].reshape(frame.current.shape)
+            frame.next[...] = rows[1].reshape(frame.next.shape)
+        else:
+            frame.current[...] = self.main_segment_lde.row(lde_step)
+            frame.next[...] = self.main_segment_lde.row(nxt)
+
+    def read_aux_trace_frame_into(self, lde_step, frame):
+        nxt = (lde_step + self._blowup) % self.trace_len()
+        seg = self.aux_segment_ldes[0]
+        frame.current[...] = seg.row(lde_step)
+        frame.next[...] = seg.row(nxt)
+
+    def get_main_segment(self):
+        return self.main_segment_lde
+
+    def get_aux_segment(self, idx):
+        return self.aux_segment_ldes[idx]
+
+
+class TracePolyTable:
+    """prover/src/trace/poly_table.rs:21-100: the trace polynomials in coefficient form (E = B here: out-of-domain points in
+    an extension field belong to the DEEP composition, which stays with the caller)."""
+
+    def __init__(self, main_trace_polys):
+        self.main_segment_polys, self.aux_segment_polys = main_trace_polys, []
+
+    def add_aux_segment(self, aux_segment_polys):
+        assert self.poly_size() == aux_segment_polys.num_rows(), \
+            "polynomials in auxiliary segment must be of the same size as in the main segment"
+        self.aux_segment_polys.append(aux_segment_polys)
+
+    def poly_size(self):
+        return self.main_segment_polys.num_rows()
+
+    def evaluate_at(self, x):
+        """ColMatrix::evaluate_columns_at of every segment (col_matrix.rs:210-216), x an element in internal representation."""
+        out = []
+        for m in [self.main_segment_polys] + self.aux_segment_polys:
+            f = m.field
+            x = np.ascontiguousarray(x, dtype=np.uint64)
+            res = np.empty((m.num_cols(),) if f == F64 else (m.num_cols(), 2), dtype=np.uint64)
+            check(lib().wg_evaluate_columns_at(f, _ptr_array(m.columns), m.num_cols(), m.num_rows(), C.c_void_p(x.ctypes.data),
+                                               C.c_void_p(res.ctypes.data)))
+            out.append(res)
+        return np.concatenate(out)
+
+    def get_ood_frame(self, z, g):
+        """[evaluate_at(z), evaluate_at(z * g)] (poly_table.rs:73-80); the caller supplies z * g (field products stay with it)."""
+        return [self.evaluate_at(z), self.evaluate_at(g)]
+
+    def main_trace_polys(self):
+        return iter(self.main_segment_polys.columns)
+
+    def num_main_trace_polys(self):
+        return self.main_segment_polys.num_cols()
+
+    def get_main_trace_poly(self, idx):
+        return self.main_segment_polys.columns[idx]
+
+
 def build_trace_commitment(hash_id, traces, domain, want_lde=True, want_polys=True):
     """traces: list of ColMatrix (one per aggregated trace, all with the same number of rows).
     Returns (list[RowMatrix], MerkleTree, list[ColMatrix]) like the reference."""

@@ -70,6 +70,51 @@ def test_device_field_ops_f64(wg):
     assert [int(x) for x in _field_op(wg, F64, 48, w, w)] == [int(x) * rinv % P64 for x in w]
 
 
+def test_device_lazy_goldilocks_ops(wg):
+    """field_lazy.cuh: the lazily reduced add / sub / canon and the products with a non-canonical first operand that the
+    decimation-in-time register network runs on. First operand ANY u64 (including [p, 2^64)), second operand <= p; results
+    are compared modulo p, `canon` and the products exactly (they must come out canonical). The two 16-point networks (the
+    canonical DIF one and the lazy DIT one) must agree element for element."""
+    rng = np.random.default_rng(21)
+    M = 2**64
+    edge_a = [0, 1, 2, P64 - 1, P64, P64 + 1, M - 1, M - 2, 2**32 - 1, 2**32, 2**32 + 1, 2**63, P64 - 2**32, 0xFFFFFFFF00000000,
+              0xFFFFFFFF00000001, 0xFFFFFFFFFFFFFFFE, 0xFFFFFFFF, 0x100000000, M - 2**32, M - 2**32 + 1]
+    edge_b = [0, 1, 2, P64 - 1, P64, P64 - 2, 2**32 - 1, 2**32, 2**32 + 1, 2**63, P64 - 2**32, 0xFFFFFFFF00000000, 0xFFFFFFFF]
+    ra = [int(x) for x in rng.integers(0, 2**64, 6000, dtype=np.uint64)]
+    rb = [int(x) % (P64 + 1) for x in rng.integers(0, 2**64, 6000, dtype=np.uint64)]
+    A = [x for x in edge_a for _ in edge_b] + ra
+    Bv = [y for _ in edge_a for y in edge_b] + rb
+    a, b = np.array(A, dtype=np.uint64), np.array(Bv, dtype=np.uint64)
+    rinv = pow(M, -1, P64)
+    for op in (96, 97):
+        assert [int(x) % P64 for x in _field_op(wg, F64, op, a, b)] == [(x + y) % P64 for x, y in zip(A, Bv)], op
+    assert [int(x) % P64 for x in _field_op(wg, F64, 98, a, b)] == [(x - y) % P64 for x, y in zip(A, Bv)]
+    assert [int(x) for x in _field_op(wg, F64, 99, a, b)] == [x % P64 for x in A]
+    # products: second operand canonical (< p)
+    Bc = [y % P64 for y in Bv]
+    bc = np.array(Bc, dtype=np.uint64)
+    for op in (100, 103):
+        assert [int(x) for x in _field_op(wg, F64, op, a, bc)] == [x * y * rinv % P64 for x, y in zip(A, Bc)], op
+    assert [int(x) for x in _field_op(wg, F64, 101, a, b)] == [x * 2**28 * rinv % P64 for x in A]
+    assert [int(x) for x in _field_op(wg, F64, 102, a, b)] == [x * 2**52 * rinv % P64 for x in A]
+    # 16-point networks: inputs canonical; thread i returns output (i & 15)
+    n = 16 * 400
+    x = np.array([int(v) % P64 for v in rng.integers(0, 2**64, n, dtype=np.uint64)], dtype=np.uint64)
+    y = np.array([int(v) % P64 for v in rng.integers(0, 2**64, n, dtype=np.uint64)], dtype=np.uint64)
+    x[:32] = [P64 - 1, 0, 1, P64 - 2] * 8
+    y[:32] = [P64 - 1] * 16 + [0] * 16
+    assert np.array_equal(_field_op(wg, F64, 112, x, y), _field_op(wg, F64, 114, x, y))
+    assert np.array_equal(_field_op(wg, F64, 113, x, y), _field_op(wg, F64, 115, x, y))
+    # and against the definition, X[k] = sum_j v_j w16^(jk) with w16 = 2^12
+    G = 0x9E3779B97F4A7C15
+    got = [int(v) for v in _field_op(wg, F64, 114, x[:64], y[:64])]
+    for i in range(64):
+        v = [((int(y[i]) if k & 1 else int(x[i])) + (k >> 1) * G) % M for k in range(16)]
+        v = [t - P64 if t >= P64 else t for t in v]
+        k = i & 15
+        assert got[i] == sum(v[j] * pow(2, 12 * j * k, P64) for j in range(16)) % P64
+
+
 def test_device_field_ops_f128(wg):
     rng = np.random.default_rng(12)
     q = fx.P128
@@ -189,6 +234,21 @@ def test_interpolate_columns_and_lde(wg, oracle, field, cols, n, blowup):
     for h in (B3, SHA3):
         leaves = lde.hash_rows(h)
         assert np.array_equal(leaves, oracle.hash_rows(field, h, want["lde"][0], n * blowup, lde.row_width, cols))
+
+
+@pytest.mark.parametrize("field", [F64, F128])
+def test_hash_rows_of_empty_rows(wg, field):
+    """hash_elements(&[]) is the digest of the empty input (crypto/src/hash/blake/mod.rs:46-59, sha/mod.rs:43-56); a FRI
+    remainder shorter than the blowup commits to exactly that (fri/src/prover/mod.rs:213-223)."""
+    import hashlib
+
+    import blake3
+
+    w = 1 if field == F64 else 2
+    m = np.zeros((5, 8 * w), dtype=np.uint64)
+    for h, want in ((B3, blake3.blake3(b"").digest()), (SHA3, hashlib.sha3_256(b"").digest())):
+        got = wg.matrix.RowMatrix(field, m.reshape(5, 8, w)[..., 0] if field == F64 else m.reshape(5, 8, 2), 8, 0).hash_rows(h)
+        assert all(bytes(r) == want for r in got), h
 
 
 @pytest.mark.parametrize("field,cols", [(F64, 1), (F64, 8), (F64, 16), (F64, 17), (F64, 100), (F64, 128), (F64, 129),
