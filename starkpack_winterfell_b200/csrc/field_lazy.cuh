@@ -25,17 +25,9 @@ struct GlLazy {
   static constexpr uint64_t P = Gl64::P;
 
   // a + b, a ANY u64, b <= p. If the 64-bit sum wraps, the true sum is s + 2^64 = s + eps (mod p), and s + eps cannot wrap
-  // again: s = a + b - 2^64 <= a - eps, so s + eps <= a. Carry mask on the ALU pipe: 4 ALU + 1 FMA instructions.
-  static __device__ __forceinline__ T add(T a, T b) {
-    uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), r0, r1;
-    asm("{\n\t.reg .u32 m;\n\t"
-        "add.cc.u32 %0, %2, %4;\n\taddc.cc.u32 %1, %3, %5;\n\tsubc.u32 m, 0, 0;\n\t"
-        "add.cc.u32 %0, %0, m;\n\t"
-        "madc.lo.u32 %1, %1, %6, 0;\n\t}"
-        : "=&r"(r0), "=&r"(r1)
-        : "r"(a0), "r"(a1), "r"(b0), "r"(b1), "r"(K_ONE));
-    return ((uint64_t)r1 << 32) | r0;
-  }
+  // again: s = a + b - 2^64 <= a - eps, so s + eps <= a. (PTX's CC.CF is the hardware carry: after an add it is the
+  // carry-out, and subc subtracts 1 - CF, so the carry word is read with addc / madc, never with subc.)
+  static __device__ __forceinline__ T add(T a, T b) { return add_b(a, b); }
   // the same with the carry word and its mask on the FMA pipe: 3 ALU + 3 FMA
   static __device__ __forceinline__ T add_b(T a, T b) {
     uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32), r0, r1;
@@ -51,15 +43,15 @@ struct GlLazy {
   // a - b, a ANY u64, b <= p: Gl64::sub's sequence is already the lazy form (borrow -> + p, which cannot wrap for b <= p)
   static __device__ __forceinline__ T sub(T a, T b) { return Gl64::sub(a, b); }
   static __device__ __forceinline__ T sub_b(T a, T b) { return Gl64::sub(a, b); }
-  // any u64 -> [0,p): a >= p exactly when a + eps wraps, and then a - p = a + eps (mod 2^64)
+  // any u64 -> [0,p): a >= p exactly when t = a + eps wraps, and then a - p = t (mod 2^64)
   static __device__ __forceinline__ T canon(T a) {
     uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), r0, r1;
-    asm("{\n\t.reg .u32 t, m;\n\t"
-        "add.cc.u32 t, %2, 0xFFFFFFFF;\n\taddc.cc.u32 t, %3, 0;\n\tsubc.u32 m, 0, 0;\n\t"
-        "add.cc.u32 %0, %2, m;\n\t"
-        "madc.lo.u32 %1, %3, %4, 0;\n\t}"
-        : "=&r"(r0), "=&r"(r1)
-        : "r"(a0), "r"(a1), "r"(K_ONE));
+    asm("{\n\t.reg .u32 t0, t1, c;\n\t.reg .pred p;\n\t"
+        "add.cc.u32 t0, %2, 0xFFFFFFFF;\n\taddc.cc.u32 t1, %3, 0;\n\taddc.u32 c, 0, 0;\n\t"
+        "setp.ne.u32 p, c, 0;\n\t"
+        "selp.u32 %0, t0, %2, p;\n\tselp.u32 %1, t1, %3, p;\n\t}"
+        : "=r"(r0), "=r"(r1)
+        : "r"(a0), "r"(a1));
     return ((uint64_t)r1 << 32) | r0;
   }
   // products and power-of-two shifts accept ANY u64 first operand (x*w < 2^64 * p keeps the Montgomery reduction exact,

@@ -35,7 +35,9 @@ constexpr int HASH_WARPS = 8;
 
 // MULTI = rows longer than one 1024-byte BLAKE3 chunk (needs the chaining-value stack)
 template <class F, int HASH, bool MULTI>
-__global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const RowHashArgs A) {
+__global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __grid_constant__ RowHashArgs A) {
+  // __grid_constant__: the per-matrix tables are indexed with a run-time matrix number; without it the 1 KB argument
+  // struct would be copied to every thread's local memory
   constexpr int SU = HASH == HASH_BLAKE3_256 ? 16 : 17;  // 8-byte units per slab
   constexpr int PITCH = 2 * SU + 1;                      // words; odd => conflict-free row reads
   __shared__ uint32_t slab_all[HASH_WARPS][32 * PITCH];
