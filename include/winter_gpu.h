@@ -10,8 +10,8 @@
  *   field 0 = f64 Goldilocks, one uint64 per element holding the MONTGOMERY word x*2^64 mod p
  *             (math/src/field/f64/mod.rs:48-53); field 1 = f128, 16 bytes little-endian canonical
  *             (math/src/field/f128/mod.rs:46-51).
- *   hash  0 = Blake3_256 (crypto/src/hash/blake/mod.rs:20-60), 1 = Sha3_256 (crypto/src/hash/sha/mod.rs:17-57).
- *   digests are 32 bytes.
+ *   hash  0 = Blake3_256 (crypto/src/hash/blake/mod.rs:20-60), 1 = Sha3_256 (crypto/src/hash/sha/mod.rs:17-57),
+ *         2 = Blake3_192 (blake/mod.rs:68-114). Digests are 32 bytes (24 for Blake3_192).
  * All functions return WG_OK (0) or a negative error code and are thread-safe. Precondition failures map to
  * the reference's assert!/MerkleTreeError conditions. There is NO CPU fallback: without a CUDA device every
  * compute entry point returns WG_ERR_CUDA.
@@ -38,7 +38,11 @@ enum {
 };
 
 enum { WG_FIELD_F64 = 0, WG_FIELD_F128 = 1 };
-enum { WG_HASH_BLAKE3_256 = 0, WG_HASH_SHA3_256 = 1 };
+/* WG_HASH_BLAKE3_192 (crypto/src/hash/blake/mod.rs:68-114): BLAKE3 truncated to 24 bytes; its digests, leaves and nodes are
+ * 24 bytes each wherever this header says "32 bytes" / "x 32". Not supported by the sharded (multi-GPU) entry points. */
+enum { WG_HASH_BLAKE3_256 = 0, WG_HASH_SHA3_256 = 1, WG_HASH_BLAKE3_192 = 2 };
+/* digest length in bytes of a hash id (0 for an unknown id) */
+uint32_t wg_digest_bytes(int hash);
 
 /* Select the CUDA device for this process (one process per GPU). Idempotent. */
 int wg_init(int device);

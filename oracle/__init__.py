@@ -12,6 +12,8 @@ import subprocess
 
 import numpy as np
 
+DIGEST = {0: 32, 1: 32, 2: 24}  # digest bytes of Blake3_256, Sha3_256, Blake3_192
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
@@ -88,11 +90,11 @@ def evaluate_poly_with_offset(field, p, offset, blowup, tw=None):
 def hash_bytes(hash_id, data: bytes) -> bytes:
     out = (C.c_uint8 * 32)()
     lib().or_hash_bytes(hash_id, data, C.c_uint64(len(data)), out)
-    return bytes(out)
+    return bytes(out)[: DIGEST[hash_id]]
 
 
 def hash_rows(field, hash_id, row_major, rows, row_width, elems_per_row):
-    leaves = np.empty((rows, 32), dtype=np.uint8)
+    leaves = np.empty((rows, DIGEST[hash_id]), dtype=np.uint8)
     rc = lib().or_hash_rows(field, hash_id, _p(np.ascontiguousarray(row_major)), C.c_uint64(rows), C.c_uint64(row_width),
                             C.c_uint64(elems_per_row), _p(leaves))
     assert rc == 0
@@ -100,9 +102,9 @@ def hash_rows(field, hash_id, row_major, rows, row_width, elems_per_row):
 
 
 def merkle_nodes(hash_id, leaves):
-    leaves = np.ascontiguousarray(leaves, dtype=np.uint8).reshape(-1, 32)
+    leaves = np.ascontiguousarray(leaves, dtype=np.uint8).reshape(-1, DIGEST[hash_id])
     n = leaves.shape[0]
-    nodes = np.empty((max(n, 1), 32), dtype=np.uint8)
+    nodes = np.empty((max(n, 1), DIGEST[hash_id]), dtype=np.uint8)
     rc = lib().or_merkle_nodes(hash_id, _p(leaves), C.c_uint64(n), _p(nodes))
     if rc:
         raise ValueError(f"or_merkle_nodes rc={rc}")
@@ -141,9 +143,9 @@ def commit_trace(field, hash_id, traces, blowup, want=("polys", "lde", "leaves",
             shp = (L, rw) if field == F64 else (L, rw, 2)
             ldes.append(np.empty(shp, dtype=np.uint64))
             lde_ptrs[i] = ldes[-1].ctypes.data
-    leaves = np.empty((L, 32), dtype=np.uint8) if "leaves" in want else None
-    nodes = np.empty((L, 32), dtype=np.uint8) if "nodes" in want else None
-    root = np.empty(32, dtype=np.uint8)
+    leaves = np.empty((L, DIGEST[hash_id]), dtype=np.uint8) if "leaves" in want else None
+    nodes = np.empty((L, DIGEST[hash_id]), dtype=np.uint8) if "nodes" in want else None
+    root = np.empty(DIGEST[hash_id], dtype=np.uint8)
     cpt = (C.c_uint32 * len(cols))(*cols)
     rc = lib().or_commit_trace(field, hash_id, C.c_uint64(n), C.c_uint64(blowup), C.c_uint32(len(traces)), cpt, col_ptrs,
                                poly_ptrs, lde_ptrs, _p(leaves), _p(nodes), _p(root))
@@ -160,7 +162,7 @@ def hash_comb_rows(field, hash_id, mats, elems):
     ptrs = (C.c_void_p * k)(*[m.ctypes.data for m in mats])
     rws = (C.c_uint64 * k)(*[m.shape[1] for m in mats])
     els = (C.c_uint64 * k)(*elems)
-    leaves = np.empty((rows, 32), dtype=np.uint8)
+    leaves = np.empty((rows, DIGEST[hash_id]), dtype=np.uint8)
     rc = lib().or_hash_comb_rows(field, hash_id, C.c_uint32(k), ptrs, rws, els, C.c_uint64(rows), _p(leaves))
     assert rc == 0
     return leaves
@@ -172,8 +174,8 @@ def fri_commit_layer(field, hash_id, evals, folding):
     n = e.shape[0]
     rows = n // folding
     tr = np.empty_like(e)
-    leaves = np.empty((rows, 32), dtype=np.uint8)
-    nodes = np.empty((rows, 32), dtype=np.uint8)
+    leaves = np.empty((rows, DIGEST[hash_id]), dtype=np.uint8)
+    nodes = np.empty((rows, DIGEST[hash_id]), dtype=np.uint8)
     rc = lib().or_fri_commit_layer(field, hash_id, _p(e), C.c_uint64(n), C.c_uint32(folding), _p(tr), _p(leaves), _p(nodes))
     if rc:
         raise ValueError(f"or_fri_commit_layer rc={rc}")

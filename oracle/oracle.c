@@ -107,7 +107,7 @@ void or_root_of_unity(int field, unsigned log_n, void* out) {
     memcpy(out, &r, 16);
   }
 }
-void or_hash_bytes(int hash, const uint8_t* in, uint64_t len, uint8_t out[32]) { oracle_hash(hash, in, len, out); }
+void or_hash_bytes(int hash, const uint8_t* in, uint64_t len, uint8_t* out) { oracle_hash(hash, in, len, out); }
 
 /* ---- math/src/fft/mod.rs:466-482 (get_twiddles), :505-522 (get_inv_twiddles) */
 int or_get_twiddles(int field, uint64_t n, int inverse, void* out) {
@@ -328,7 +328,7 @@ static size_t row_bytes(int field, const void* row, uint64_t elems, uint8_t* dst
  * (row_matrix.rs:183-203). ldes[t] is row-major rows x row_widths[t]; only elems[t] are hashed. */
 int or_hash_comb_rows(int field, int hash, uint32_t n_traces, const void* const* ldes, const uint64_t* row_widths,
                       const uint64_t* elems, uint64_t rows, uint8_t* leaves_out) {
-  size_t es = esize(field), total = 0;
+  size_t es = esize(field), total = 0, dl = oracle_digest_len(hash);
   for (uint32_t t = 0; t < n_traces; t++) total += elems[t] * es;
 #pragma omp parallel
   {
@@ -338,7 +338,7 @@ int or_hash_comb_rows(int field, int hash, uint32_t n_traces, const void* const*
       size_t pos = 0;
       for (uint32_t t = 0; t < n_traces; t++)
         pos += row_bytes(field, (const uint8_t*)ldes[t] + r * row_widths[t] * es, elems[t], buf + pos);
-      oracle_hash(hash, buf, pos, leaves_out + 32 * r);
+      oracle_hash(hash, buf, pos, leaves_out + dl * r);
     }
     free(buf);
   }
@@ -355,12 +355,13 @@ int or_merkle_nodes(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t*
   if (n_leaves < 2) return OR_ERR_TOO_FEW;
   if (!is_pow2(n_leaves)) return OR_ERR_NOT_POW2;
   uint64_t n = n_leaves / 2;
-  memset(nodes, 0, 32);
+  size_t dl = oracle_digest_len(hash); /* merge = hash of the 2*dl bytes of the two children (blake/mod.rs:31-33,85-88) */
+  memset(nodes, 0, dl);
 #pragma omp parallel for schedule(static)
-  for (uint64_t i = 0; i < n; i++) oracle_hash(hash, leaves + 64 * i, 64, nodes + 32 * (n + i));
+  for (uint64_t i = 0; i < n; i++) oracle_hash(hash, leaves + 2 * dl * i, 2 * dl, nodes + dl * (n + i));
   for (uint64_t lvl = n / 2; lvl >= 1; lvl /= 2) {
 #pragma omp parallel for schedule(static) if (lvl >= 1024)
-    for (uint64_t i = lvl; i < 2 * lvl; i++) oracle_hash(hash, nodes + 64 * i, 64, nodes + 32 * i);
+    for (uint64_t i = lvl; i < 2 * lvl; i++) oracle_hash(hash, nodes + 2 * dl * i, 2 * dl, nodes + dl * i);
   }
   return OR_OK;
 }
@@ -396,11 +397,11 @@ int or_commit_trace(int field, int hash, uint64_t n, uint64_t blowup, uint32_t n
                                 field == 0 ? (const void*)&gen64 : (const void*)&gen128, tw, ldes[t]);
     c0 += cols_per_trace[t];
   }
-  uint8_t* leaves = leaves_out ? leaves_out : (uint8_t*)malloc(32 * L);
+  uint8_t* leaves = leaves_out ? leaves_out : (uint8_t*)malloc(32 * L); /* 32 >= any digest length */
   uint8_t* nodes = nodes_out ? nodes_out : (uint8_t*)malloc(32 * L);
   if (!rc) rc = or_hash_comb_rows(field, hash, n_traces, (const void* const*)ldes, rw, el, L, leaves);
   if (!rc) rc = or_merkle_nodes(hash, leaves, L, nodes);
-  if (!rc) memcpy(root_out, nodes + 32, 32);
+  if (!rc) memcpy(root_out, nodes + oracle_digest_len(hash), oracle_digest_len(hash));
   if (!leaves_out) free(leaves);
   if (!nodes_out) free(nodes);
   for (uint32_t t = 0; t < n_traces; t++)

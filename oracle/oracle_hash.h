@@ -165,8 +165,18 @@ static inline void oracle_sha3_256(const uint8_t* in, size_t len, uint8_t out[32
 
 /* hash ids shared with include/winter_gpu.h */
 enum { OR_HASH_BLAKE3_256 = 0, OR_HASH_SHA3_256 = 1, OR_HASH_BLAKE3_192 = 2 };
-static inline void oracle_hash(int hash, const uint8_t* in, size_t len, uint8_t out[32]) {
-  if (hash == OR_HASH_SHA3_256) oracle_sha3_256(in, len, out);
-  else oracle_blake3_256(in, len, out);
+/* digest length: Blake3_192 keeps the first 24 bytes of the BLAKE3 output (crypto/src/hash/blake/mod.rs:71-83) */
+static inline size_t oracle_digest_len(int hash) { return hash == OR_HASH_BLAKE3_192 ? 24 : 32; }
+/* writes oracle_digest_len(hash) bytes */
+static inline void oracle_hash(int hash, const uint8_t* in, size_t len, uint8_t* out) {
+  if (hash == OR_HASH_SHA3_256) {
+    oracle_sha3_256(in, len, out);
+  } else if (hash == OR_HASH_BLAKE3_192) {
+    uint8_t full[32];
+    oracle_blake3_256(in, len, full);
+    memcpy(out, full, 24);
+  } else {
+    oracle_blake3_256(in, len, out);
+  }
 }
 #endif

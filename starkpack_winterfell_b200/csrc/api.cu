@@ -70,6 +70,8 @@ static cudaError_t dev_malloc(void** p, size_t bytes) {
 }
 
 static inline bool is_pow2(uint64_t n) { return n && !(n & (n - 1)); }
+static inline size_t dlen(int hash) { return (size_t)hash_digest_bytes(hash); }  // 24 for Blake3_192, else 32
+static inline bool hash_ok(int hash) { return hash == WG_HASH_BLAKE3_256 || hash == WG_HASH_SHA3_256 || hash == WG_HASH_BLAKE3_192; }
 static inline int ilog2(uint64_t n) { return 63 - __builtin_clzll(n); }
 
 static int ensure_device() {
@@ -583,7 +585,7 @@ template <class F>
 static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes, const uint64_t* row_widths,
                          const uint64_t* elems, uint64_t rows, uint8_t* d_leaves, cudaStream_t stream) {
   if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
-  if (hash != WG_HASH_BLAKE3_256 && hash != WG_HASH_SHA3_256) return fail(WG_ERR_ARG, "unknown hash %d", hash);
+  if (!hash_ok(hash)) return fail(WG_ERR_ARG, "unknown hash %d", hash);
   if (rows == 0) return WG_OK;
   RowHashArgs a;
   memset(&a, 0, sizeof a);
@@ -609,6 +611,11 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
       hash_rows_kernel<F, HASH_BLAKE3_256, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
     else
       hash_rows_kernel<F, HASH_BLAKE3_256, true><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+  } else if (hash == WG_HASH_BLAKE3_192) {
+    if (off * 8 <= 1024)
+      hash_rows_kernel<F, HASH_BLAKE3_192, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+    else
+      hash_rows_kernel<F, HASH_BLAKE3_192, true><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
   } else {
     hash_rows_kernel<F, HASH_SHA3_256, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
   }
@@ -619,14 +626,15 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
 
 template <int HASH>
 static int merkle_dev_t(const uint8_t* d_leaves, uint64_t n_leaves, uint8_t* d_nodes, cudaStream_t stream) {
-  uint4* nodes = reinterpret_cast<uint4*>(d_nodes);
+  constexpr int U = DigestCfg<HASH>::U;  // 8-byte units per digest
+  uint2* nodes = reinterpret_cast<uint2*>(d_nodes);
   uint64_t n = n_leaves / 2;
   ProfScope ps(PH_MERKLE, stream);
-  merkle_level_kernel<HASH><<<cdiv(n, 256), 256, 0, stream>>>(reinterpret_cast<const uint4*>(d_leaves), nodes + 2 * n, n, 1u);
+  merkle_level_kernel<HASH><<<cdiv(n, 256), 256, 0, stream>>>(reinterpret_cast<const uint2*>(d_leaves), nodes + U * n, n, 1u);
   CUDA_TRY(cudaGetLastError());
   g_launches++;
   while (n > 1024) {
-    merkle_level_kernel<HASH><<<cdiv(n / 2, 256), 256, 0, stream>>>(nodes + 2 * n, nodes + n, n / 2, 1u);
+    merkle_level_kernel<HASH><<<cdiv(n / 2, 256), 256, 0, stream>>>(nodes + U * n, nodes + U * (n / 2), n / 2, 1u);
     CUDA_TRY(cudaGetLastError());
     g_launches++;
     n /= 2;
@@ -642,6 +650,7 @@ static int merkle_dev(int hash, const uint8_t* d_leaves, uint64_t n_leaves, uint
   if (!is_pow2(n_leaves)) return fail(WG_ERR_NOT_POW2, "number of leaves %llu is not a power of two", (unsigned long long)n_leaves);
   if (hash == WG_HASH_BLAKE3_256) return merkle_dev_t<HASH_BLAKE3_256>(d_leaves, n_leaves, d_nodes, stream);
   if (hash == WG_HASH_SHA3_256) return merkle_dev_t<HASH_SHA3_256>(d_leaves, n_leaves, d_nodes, stream);
+  if (hash == WG_HASH_BLAKE3_192) return merkle_dev_t<HASH_BLAKE3_192>(d_leaves, n_leaves, d_nodes, stream);
   return fail(WG_ERR_ARG, "unknown hash %d", hash);
 }
 
@@ -996,11 +1005,11 @@ static int h_hash_rows(int hash, const void* rows_host, uint64_t rows, uint64_t 
   typedef typename F::T T;
   DevBuf m, l;
   WG_TRY(m.alloc(rows * row_width * sizeof(T)));
-  WG_TRY(l.alloc(rows * 32));
+  WG_TRY(l.alloc(rows * dlen(hash)));
   CUDA_TRY(cudaMemcpyAsync(m.p, rows_host, rows * row_width * sizeof(T), cudaMemcpyHostToDevice, 0));
   const void* ptrs[1] = {m.p};
   WG_TRY(hash_rows_dev<F>(hash, 1, ptrs, &row_width, &elems, rows, l.as<uint8_t>(), 0));
-  CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * dlen(hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -1057,7 +1066,7 @@ static int h_hash_comb_rows(int hash, uint32_t n_traces, const void* const* mats
   DevBuf l;
   std::vector<const void*> ptrs(n_traces);
   LegacyStreamDrainFwd drain;
-  WG_TRY(l.alloc(rows * 32));
+  WG_TRY(l.alloc(rows * dlen(hash)));
   for (uint32_t t = 0; t < n_traces; t++) {
     if (!mats[t]) return fail(WG_ERR_ARG, "null matrix %u", t);
     WG_TRY(d[t].alloc(rows * rws[t] * sizeof(T)));
@@ -1065,7 +1074,7 @@ static int h_hash_comb_rows(int hash, uint32_t n_traces, const void* const* mats
     ptrs[t] = d[t].p;
   }
   WG_TRY(hash_rows_dev<F>(hash, n_traces, ptrs.data(), rws, els, rows, l.as<uint8_t>(), 0));
-  CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaMemcpyAsync(leaves, l.p, rows * dlen(hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -1150,7 +1159,7 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   const uint64_t se2 = lde_scratch_elems<F>((uint32_t)max_cols, n, blowup);
   if (se2 > se) se = se2;
   auto al = [](size_t b) { return (b + 255) / 256 * 256; };
-  size_t need = 2 * al(colb * total_cols) + 2 * al(L * 32) + al(se * sizeof(T) + 16);
+  size_t need = 2 * al(colb * total_cols) + 2 * al(L * dlen(hash)) + al(se * sizeof(T) + 16);
   for (uint32_t t = 0; t < n_traces; t++) need += al(L * ((uint64_t)(cols_per_trace[t] + 7) / 8 * 8) * sizeof(T));
   std::lock_guard<std::mutex> lk(g_commit_mu);
   WG_TRY(arena_reserve(need));
@@ -1162,8 +1171,8 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   };
   T* cols = (T*)take(colb * total_cols);
   T* polys = (T*)take(colb * total_cols);
-  uint8_t* leaves = (uint8_t*)take(L * 32);
-  uint8_t* nodes = (uint8_t*)take(L * 32);
+  uint8_t* leaves = (uint8_t*)take(L * dlen(hash));
+  uint8_t* nodes = (uint8_t*)take(L * dlen(hash));
   T* scr = (T*)take(se * sizeof(T) + 16);
   std::vector<T*> ldes(n_traces);
   std::vector<uint64_t> rws(n_traces), els(n_traces);
@@ -1206,9 +1215,9 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   WG_TRY(merkle_dev(hash, leaves, L, nodes, sc));
   CUDA_TRY(cudaEventRecord(g_ev[2], sc));
   CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[2], 0));
-  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes + 32, 32, cudaMemcpyDeviceToHost, sx));
-  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves, L * 32, cudaMemcpyDeviceToHost, sx));
-  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes, L * 32, cudaMemcpyDeviceToHost, sx));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes + dlen(hash), dlen(hash), cudaMemcpyDeviceToHost, sx));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves, L * dlen(hash), cudaMemcpyDeviceToHost, sx));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes, L * dlen(hash), cudaMemcpyDeviceToHost, sx));
   CUDA_TRY(cudaStreamSynchronize(sx));
   CUDA_TRY(cudaStreamSynchronize(sc));
   CUDA_TRY(cudaStreamSynchronize(sh));
@@ -1242,8 +1251,8 @@ static int h_commit_trace_ext(int hash, uint32_t deg, uint64_t n, uint64_t blowu
   const uint64_t se2 = lde_scratch_elems<F>((uint32_t)(max_cols * deg), n, blowup);
   if (se2 > se) se = se2;
   WG_TRY(scr.alloc(se * sizeof(T)));
-  WG_TRY(leaves.alloc(L * 32));
-  WG_TRY(nodes.alloc(L * 32));
+  WG_TRY(leaves.alloc(L * dlen(hash)));
+  WG_TRY(nodes.alloc(L * dlen(hash)));
   std::vector<DevBuf> ldes(n_traces);
   std::vector<uint64_t> rws(n_traces), els(n_traces);
   std::vector<const void*> lde_c(n_traces);
@@ -1265,9 +1274,9 @@ static int h_commit_trace_ext(int hash, uint32_t deg, uint64_t n, uint64_t blowu
   WG_TRY(hash_rows_dev<F>(hash, n_traces, lde_c.data(), rws.data(), els.data(), L, leaves.as<uint8_t>(), 0));
   WG_TRY(merkle_dev(hash, leaves.as<uint8_t>(), L, nodes.as<uint8_t>(), 0));
   if (polys_out) WG_TRY(download_columns<T>(polys_out, (uint32_t)total, n, deg, polys.as<T>(), cols.as<T>(), 0));
-  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes.as<uint8_t>() + 32, 32, cudaMemcpyDeviceToHost, 0));
-  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves.p, L * 32, cudaMemcpyDeviceToHost, 0));
-  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes.p, L * 32, cudaMemcpyDeviceToHost, 0));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, nodes.as<uint8_t>() + dlen(hash), dlen(hash), cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, leaves.p, L * dlen(hash), cudaMemcpyDeviceToHost, 0));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, nodes.p, L * dlen(hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -1324,8 +1333,8 @@ struct Commitment {
   size_t lde_bytes(size_t t) const { return L * rws[t] * (field == WG_FIELD_F64 ? 8 : 16); }
   ~Commitment() {
     for (size_t t = 0; t < ldes.size(); t++) cached_free(ldes[t], lde_bytes(t));
-    cached_free(leaves, L * 32);
-    cached_free(nodes, L * 32);
+    cached_free(leaves, L * dlen(hash));
+    cached_free(nodes, L * dlen(hash));
   }
 };
 
@@ -1337,7 +1346,7 @@ static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool
   const uint32_t n_traces = (uint32_t)cm->cols.size();
   WG_TRY(check_domain<F>(n, blowup));
   if (n_traces == 0 || n_traces > HASH_MAX_TRACES) return fail(WG_ERR_UNSUPPORTED, "1..%d aggregated traces supported", HASH_MAX_TRACES);
-  if (cm->hash != WG_HASH_BLAKE3_256 && cm->hash != WG_HASH_SHA3_256) return fail(WG_ERR_ARG, "unknown hash %d", cm->hash);
+  if (!hash_ok(cm->hash)) return fail(WG_ERR_ARG, "unknown hash %d", cm->hash);
   uint64_t total_cols = 0, max_cols = 0;
   for (uint32_t c : cm->cols) {
     if (c == 0) return fail(WG_ERR_ARG, "a trace has no columns");
@@ -1353,8 +1362,8 @@ static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool
     cm->rws[t] = (uint64_t)(cm->cols[t] + 7) / 8 * 8;
     WG_TRY(dmalloc(&cm->ldes[t], L * cm->rws[t] * sizeof(T)));
   }
-  WG_TRY(dmalloc((void**)&cm->leaves, L * 32));
-  WG_TRY(dmalloc((void**)&cm->nodes, L * 32));
+  WG_TRY(dmalloc((void**)&cm->leaves, L * dlen(cm->hash)));
+  WG_TRY(dmalloc((void**)&cm->nodes, L * dlen(cm->hash)));
   // temporaries from the shared arena
   uint64_t se = inputs_are_polys ? 0 : interpolate_scratch_elems<F>((uint32_t)(total_cols < 65535 ? total_cols : 65535), n);
   // LDE scratch: whole matrix when it fits next to everything else, else 8-column sweeps
@@ -1406,7 +1415,7 @@ static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool
   }
   WG_TRY(hash_rows_dev<F>(cm->hash, n_traces, lde_c.data(), cm->rws.data(), els.data(), L, cm->leaves, sc));
   WG_TRY(merkle_dev(cm->hash, cm->leaves, L, cm->nodes, sc));
-  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, cm->nodes + 32, 32, cudaMemcpyDeviceToHost, sc));
+  if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, cm->nodes + dlen(cm->hash), dlen(cm->hash), cudaMemcpyDeviceToHost, sc));
   CUDA_TRY(cudaStreamSynchronize(sc));
   CUDA_TRY(cudaStreamSynchronize(sx));
   CUDA_TRY(cudaStreamSynchronize(sh));
@@ -1445,10 +1454,11 @@ __global__ void gather_rows_kernel(const uint64_t* lde, uint64_t rw_words, uint3
   const uint32_t p = (uint32_t)(i / elem_words), e = (uint32_t)(i % elem_words);
   out[i] = lde[pos[p] * rw_words + e];
 }
-__global__ void gather_digests_kernel(const uint4* src, const uint64_t* idx, uint32_t n, uint4* out) {
+// digests of `units` 8-byte words each (4 for the 32-byte hashes, 3 for Blake3_192)
+__global__ void gather_digests_kernel(const uint2* src, const uint64_t* idx, uint32_t n, uint32_t units, uint2* out) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 2 * n) return;
-  out[i] = src[2 * idx[i >> 1] + (i & 1)];
+  if (i >= units * n) return;
+  out[i] = src[units * idx[i / units] + (i % units)];
 }
 
 // ------------------------------------------------------------------------------------------------ FRI layers
@@ -1525,13 +1535,13 @@ static int h_fri_commit_layer(int hash, const void* evals, uint64_t n, uint32_t 
   DevBuf e, t, l, nd;
   WG_TRY(e.alloc(n * sizeof(T)));
   WG_TRY(t.alloc(n * sizeof(T)));
-  WG_TRY(l.alloc(rows * 32));
-  WG_TRY(nd.alloc(rows * 32));
+  WG_TRY(l.alloc(rows * dlen(hash)));
+  WG_TRY(nd.alloc(rows * dlen(hash)));
   CUDA_TRY(cudaMemcpyAsync(e.p, evals, n * sizeof(T), cudaMemcpyHostToDevice, 0));
   WG_TRY(fri_commit_layer_dev<F>(hash, e.as<T>(), n, ff, t.as<T>(), l.as<uint8_t>(), nd.as<uint8_t>(), 0));
   if (transposed_out) CUDA_TRY(cudaMemcpyAsync(transposed_out, t.p, n * sizeof(T), cudaMemcpyDeviceToHost, 0));
-  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, l.p, rows * 32, cudaMemcpyDeviceToHost, 0));
-  CUDA_TRY(cudaMemcpyAsync(nodes_out, nd.p, rows * 32, cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, l.p, rows * dlen(hash), cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaMemcpyAsync(nodes_out, nd.p, rows * dlen(hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -1593,6 +1603,7 @@ int wg_shutdown(void) {
 }
 
 const char* wg_last_error(void) { return g_last_error.c_str(); }
+uint32_t wg_digest_bytes(int hash) { return hash_ok(hash) ? (uint32_t)dlen(hash) : 0u; }
 uint64_t wg_launch_count(void) { return g_launches.load(); }
 
 int wg_debug_field_op(int field, int op, const void* a, const void* b, void* out, uint32_t n) {
@@ -1716,11 +1727,11 @@ int wg_merkle_new(int hash, const uint8_t* leaves, uint64_t n_leaves, uint8_t* n
   if (!is_pow2(n_leaves)) return fail(WG_ERR_NOT_POW2, "number of leaves %llu is not a power of two", (unsigned long long)n_leaves);
   WG_TRY(ensure_device());
   DevBuf l, nd;
-  WG_TRY(l.alloc(n_leaves * 32));
-  WG_TRY(nd.alloc(n_leaves * 32));
-  CUDA_TRY(cudaMemcpyAsync(l.p, leaves, n_leaves * 32, cudaMemcpyHostToDevice, 0));
+  WG_TRY(l.alloc(n_leaves * dlen(hash)));
+  WG_TRY(nd.alloc(n_leaves * dlen(hash)));
+  CUDA_TRY(cudaMemcpyAsync(l.p, leaves, n_leaves * dlen(hash), cudaMemcpyHostToDevice, 0));
   WG_TRY(merkle_dev(hash, l.as<uint8_t>(), n_leaves, nd.as<uint8_t>(), 0));
-  CUDA_TRY(cudaMemcpyAsync(nodes_out, nd.p, n_leaves * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaMemcpyAsync(nodes_out, nd.p, n_leaves * dlen(hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -1792,13 +1803,14 @@ int wg_commitment_digests(const void* handle, int which, uint32_t n, const uint6
   WG_TRY(ensure_device());
   DevBuf didx, dout;
   WG_TRY(didx.alloc(n * 8));
-  WG_TRY(dout.alloc((size_t)n * 32));
+  WG_TRY(dout.alloc((size_t)n * dlen(cm->hash)));
   CUDA_TRY(cudaMemcpyAsync(didx.p, indexes, n * 8, cudaMemcpyHostToDevice, 0));
-  gather_digests_kernel<<<cdiv(2 * (uint64_t)n, 256), 256, 0, 0>>>((const uint4*)(which ? cm->nodes : cm->leaves), didx.as<uint64_t>(), n,
-                                                                  dout.as<uint4>());
+  const uint32_t units = (uint32_t)dlen(cm->hash) / 8;
+  gather_digests_kernel<<<cdiv(units * (uint64_t)n, 256), 256, 0, 0>>>((const uint2*)(which ? cm->nodes : cm->leaves), didx.as<uint64_t>(), n,
+                                                                      units, dout.as<uint2>());
   CUDA_TRY(cudaGetLastError());
   g_launches++;
-  CUDA_TRY(cudaMemcpyAsync(out, dout.p, (size_t)n * 32, cudaMemcpyDeviceToHost, 0));
+  CUDA_TRY(cudaMemcpyAsync(out, dout.p, (size_t)n * dlen(cm->hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -1822,8 +1834,8 @@ int wg_commitment_download(const void* handle, void* const* lde_out, uint8_t* le
   const size_t es = cm->field == WG_FIELD_F64 ? 8 : 16;
   for (size_t t = 0; lde_out && t < cm->cols.size(); t++)
     if (lde_out[t]) CUDA_TRY(cudaMemcpyAsync(lde_out[t], cm->ldes[t], cm->L * cm->rws[t] * es, cudaMemcpyDeviceToHost, 0));
-  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, cm->leaves, cm->L * 32, cudaMemcpyDeviceToHost, 0));
-  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, cm->nodes, cm->L * 32, cudaMemcpyDeviceToHost, 0));
+  if (leaves_out) CUDA_TRY(cudaMemcpyAsync(leaves_out, cm->leaves, cm->L * dlen(cm->hash), cudaMemcpyDeviceToHost, 0));
+  if (nodes_out) CUDA_TRY(cudaMemcpyAsync(nodes_out, cm->nodes, cm->L * dlen(cm->hash), cudaMemcpyDeviceToHost, 0));
   CUDA_TRY(cudaStreamSynchronize(0));
   return WG_OK;
 }
@@ -2264,7 +2276,7 @@ int wg_sharded_digests(const void* handle, int which, uint32_t n, const uint64_t
   WG_TRY(dout.alloc((size_t)n * 32));
   LegacyStreamDrain drain;
   CUDA_TRY(cudaMemcpyAsync(didx.p, indexes, n * 8, cudaMemcpyHostToDevice, 0));
-  gather_digests_kernel<<<cdiv(2 * (uint64_t)n, 256), 256, 0, 0>>>((const uint4*)(which ? h->nodes : h->leaves), didx.as<uint64_t>(), n, dout.as<uint4>());
+  gather_digests_kernel<<<cdiv(4 * (uint64_t)n, 256), 256, 0, 0>>>((const uint2*)(which ? h->nodes : h->leaves), didx.as<uint64_t>(), n, 4u, dout.as<uint2>());
   CUDA_TRY(cudaGetLastError());
   g_launches++;
   CUDA_TRY(cudaMemcpyAsync(out, dout.p, (size_t)n * 32, cudaMemcpyDeviceToHost, 0));

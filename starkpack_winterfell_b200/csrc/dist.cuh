@@ -299,6 +299,7 @@ static int shard_alloc_outputs(ShardedCommit* h, bool own_polys, uint32_t my_col
 
 static int shard_check_shape(int field, int hash, uint64_t n, uint64_t blowup, uint32_t total_cols, uint32_t world) {
   if (field != WG_FIELD_F64 && field != WG_FIELD_F128) return fail(WG_ERR_ARG, "unknown field id %d", field);
+  if (hash == WG_HASH_BLAKE3_192) return fail(WG_ERR_UNSUPPORTED, "Blake3_192 is not supported by the sharded entry points");
   if (hash != WG_HASH_BLAKE3_256 && hash != WG_HASH_SHA3_256) return fail(WG_ERR_ARG, "unknown hash %d", hash);
   if (!is_pow2(world)) return fail(WG_ERR_ARG, "number of ranks %u must be a power of two", world);
   if (total_cols < world) return fail(WG_ERR_ARG, "more ranks (%u) than columns (%u)", world, total_cols);

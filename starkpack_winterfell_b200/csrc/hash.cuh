@@ -11,7 +11,10 @@
 
 namespace wg {
 
-enum { HASH_BLAKE3_256 = 0, HASH_SHA3_256 = 1 };
+// Blake3_192 (crypto/src/hash/blake/mod.rs:68-114) is BLAKE3 truncated to its first 24 bytes; merge hashes the 48 bytes of
+// two truncated digests.
+enum { HASH_BLAKE3_256 = 0, HASH_SHA3_256 = 1, HASH_BLAKE3_192 = 2 };
+WG_HD constexpr int hash_digest_bytes(int hash) { return hash == HASH_BLAKE3_192 ? 24 : 32; }
 
 // ------------------------------------------------------------------------------------------------ BLAKE3
 enum { B3_CHUNK_START = 1, B3_CHUNK_END = 2, B3_PARENT = 4, B3_ROOT = 8 };
@@ -115,6 +118,17 @@ WG_HD void b3_parent(const uint32_t left[8], uint32_t right_inout[8], uint32_t e
 WG_HD void b3_merge(const uint32_t in16[16], uint32_t out[8], uint32_t one = 1) {
   b3_iv(out);
   b3_compress(out, in16, 0, 64, B3_CHUNK_START | B3_CHUNK_END | B3_ROOT, one);
+}
+
+// Blake3_192 merge: hash(left24 || right24), one 48-byte block; the caller keeps the first 6 output words
+WG_HD void b3_merge48(const uint32_t in12[12], uint32_t out[8], uint32_t one = 1) {
+  uint32_t m[16];
+#pragma unroll
+  for (int i = 0; i < 12; i++) m[i] = in12[i];
+#pragma unroll
+  for (int i = 12; i < 16; i++) m[i] = 0;
+  b3_iv(out);
+  b3_compress(out, m, 0, 48, B3_CHUNK_START | B3_CHUNK_END | B3_ROOT, one);
 }
 
 // Streaming BLAKE3 over an input of known length: feed() takes consecutive 64-byte blocks (zero padded).
@@ -294,7 +308,7 @@ WG_HD void sha3_256_lanes(LD64 ld64, uint32_t nbytes, uint32_t out[8]) {
 // Generic front-end: digest of a word stream with either hash.
 template <class LD>
 WG_HD void hash_words(int hash, LD ld, uint32_t nbytes, uint32_t out[8]) {
-  if (hash == HASH_BLAKE3_256) {
+  if (hash == HASH_BLAKE3_256 || hash == HASH_BLAKE3_192) {
     b3_hash_words(ld, nbytes, out);
   } else {
     sha3_256_lanes([&](uint32_t i) { return (uint64_t)ld(2 * i) | ((uint64_t)ld(2 * i + 1) << 32); }, nbytes, out);

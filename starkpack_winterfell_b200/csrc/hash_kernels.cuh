@@ -38,7 +38,8 @@ template <class F, int HASH, bool MULTI>
 __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __grid_constant__ RowHashArgs A) {
   // __grid_constant__: the per-matrix tables are indexed with a run-time matrix number; without it the 1 KB argument
   // struct would be copied to every thread's local memory
-  constexpr int SU = HASH == HASH_BLAKE3_256 ? 16 : 17;  // 8-byte units per slab
+  constexpr bool IS_B3 = HASH != HASH_SHA3_256;  // Blake3_256 and its 24-byte truncation Blake3_192
+  constexpr int SU = IS_B3 ? 16 : 17;             // 8-byte units per slab
   constexpr int PITCH = 2 * SU + 1;                      // words; odd => conflict-free row reads
   __shared__ uint32_t slab_all[HASH_WARPS][32 * PITCH];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -50,7 +51,7 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
 
   B3StreamT<MULTI> b3;
   uint64_t ks[25];
-  if (HASH == HASH_BLAKE3_256) {
+  if (IS_B3) {
     b3.init(nbytes, A.one);
   } else {
 #pragma unroll
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
   bool sha_done = false;
 
   // an empty row still takes one (padding-only) block: the digest of the empty input
-  for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done) || (HASH == HASH_BLAKE3_256 && nbytes == 0 && u0 == 0);
+  for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done) || (IS_B3 && nbytes == 0 && u0 == 0);
        u0 += SU) {
     // ---- stage SU units of each of the warp's 32 rows: issue all SU loads first (one long-scoreboard wait per
     // slab instead of one per element), then convert and store
@@ -92,7 +93,7 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
     __syncwarp();
     // ---- consume: lane owns row `lane`
     const uint32_t* my = slab + lane * PITCH;
-    if (HASH == HASH_BLAKE3_256) {
+    if (IS_B3) {
 #pragma unroll 1
       for (int b = 0; b < 2; b++) {
         if ((u0 + 8 * b) * 8 < nbytes || (nbytes == 0 && b == 0)) {
@@ -121,7 +122,12 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
   const uint64_t row = row0 + lane;
   if (row < A.rows) {
     uint4* dst = reinterpret_cast<uint4*>(A.leaves + row * 32);
-    if (HASH == HASH_BLAKE3_256) {
+    if (HASH == HASH_BLAKE3_192) {
+      uint2* d24 = reinterpret_cast<uint2*>(A.leaves + row * 24);  // first 24 bytes of the BLAKE3 output
+      d24[0] = make_uint2(b3.cv[0], b3.cv[1]);
+      d24[1] = make_uint2(b3.cv[2], b3.cv[3]);
+      d24[2] = make_uint2(b3.cv[4], b3.cv[5]);
+    } else if (HASH == HASH_BLAKE3_256) {
       dst[0] = make_uint4(b3.cv[0], b3.cv[1], b3.cv[2], b3.cv[3]);
       dst[1] = make_uint4(b3.cv[4], b3.cv[5], b3.cv[6], b3.cv[7]);
     } else {
@@ -132,61 +138,66 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
 }
 
 // ---------------------------------------------------------------------------------------------- Merkle
+// Digests are DW 32-bit words (8 for the 32-byte hashes, 6 for Blake3_192); nodes are addressed in 8-byte units so both
+// sizes share the kernels: digest i starts at unit i * DW / 2.
 template <int HASH>
-__device__ __forceinline__ void merge64(const uint32_t in16[16], uint32_t out[8], uint32_t one) {
-  if (HASH == HASH_BLAKE3_256) {
-    b3_merge(in16, out, one);
-  } else {
-    sha3_256_lanes([&](uint32_t i) { return (uint64_t)in16[2 * i] | ((uint64_t)in16[2 * i + 1] << 32); }, 64, out);
+struct DigestCfg {
+  static constexpr int DW = hash_digest_bytes(HASH) / 4;
+  static constexpr int U = DW / 2;  // 8-byte units per digest
+};
+
+// out = H(left || right) for the two consecutive digests at `pair`
+template <int HASH>
+__device__ __forceinline__ void merge_pair(const uint2* __restrict__ pair, uint32_t out[8], uint32_t one) {
+  constexpr int U = DigestCfg<HASH>::U;
+  uint32_t m[16];
+#pragma unroll
+  for (int k = 0; k < 2 * U; k++) {
+    const uint2 v = pair[k];
+    m[2 * k] = v.x;
+    m[2 * k + 1] = v.y;
   }
+  if (HASH == HASH_BLAKE3_256) {
+    b3_merge(m, out, one);
+  } else if (HASH == HASH_BLAKE3_192) {
+    b3_merge48(m, out, one);
+  } else {
+    sha3_256_lanes([&](uint32_t i) { return (uint64_t)m[2 * i] | ((uint64_t)m[2 * i + 1] << 32); }, 64, out);
+  }
+}
+template <int HASH>
+__device__ __forceinline__ void store_digest(uint2* dst, const uint32_t o[8]) {
+#pragma unroll
+  for (int k = 0; k < DigestCfg<HASH>::U; k++) dst[k] = make_uint2(o[2 * k], o[2 * k + 1]);
 }
 
 // parents[i] = H(children[2i] || children[2i+1]), i < n_parents
 template <int HASH>
-__global__ void __launch_bounds__(256) merkle_level_kernel(const uint4* __restrict__ children, uint4* __restrict__ parents,
+__global__ void __launch_bounds__(256) merkle_level_kernel(const uint2* __restrict__ children, uint2* __restrict__ parents,
                                                            uint64_t n_parents, uint32_t one) {
+  constexpr int U = DigestCfg<HASH>::U;
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_parents) return;
-  uint32_t m[16], o[8];
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    uint4 v = children[4 * i + k];
-    m[4 * k] = v.x;
-    m[4 * k + 1] = v.y;
-    m[4 * k + 2] = v.z;
-    m[4 * k + 3] = v.w;
-  }
-  merge64<HASH>(m, o, one);
-  parents[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
-  parents[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+  uint32_t o[8];
+  merge_pair<HASH>(children + 2 * U * i, o, one);
+  store_digest<HASH>(parents + U * i, o);
 }
 
 // Finishes the tree in one block: nodes[n .. 2n) hold level n (n <= 1024 a power of two); computes
 // nodes[n/2 .. n), ..., nodes[1], and zeroes nodes[0].
 template <int HASH>
-__global__ void __launch_bounds__(512) merkle_top_kernel(uint4* nodes, uint32_t n, uint32_t one) {
+__global__ void __launch_bounds__(512) merkle_top_kernel(uint2* nodes, uint32_t n, uint32_t one) {
+  constexpr int U = DigestCfg<HASH>::U;
   for (uint32_t lvl = n / 2; lvl >= 1; lvl >>= 1) {
     for (uint32_t i = threadIdx.x; i < lvl; i += blockDim.x) {
       const uint32_t node = lvl + i;
-      uint32_t m[16], o[8];
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        uint4 v = nodes[2 * (2 * node) + k];
-        m[4 * k] = v.x;
-        m[4 * k + 1] = v.y;
-        m[4 * k + 2] = v.z;
-        m[4 * k + 3] = v.w;
-      }
-      merge64<HASH>(m, o, one);
-      nodes[2 * node] = make_uint4(o[0], o[1], o[2], o[3]);
-      nodes[2 * node + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+      uint32_t o[8];
+      merge_pair<HASH>(nodes + (size_t)U * (2 * node), o, one);
+      store_digest<HASH>(nodes + (size_t)U * node, o);
     }
     __syncthreads();
   }
-  if (threadIdx.x == 0) {
-    nodes[0] = make_uint4(0, 0, 0, 0);
-    nodes[1] = make_uint4(0, 0, 0, 0);
-  }
+  if (threadIdx.x < U) nodes[threadIdx.x] = make_uint2(0, 0);
 }
 
 }  // namespace wg

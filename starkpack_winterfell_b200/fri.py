@@ -12,7 +12,7 @@ import ctypes as C
 import numpy as np
 
 from . import fft
-from ._lib import ELEM_BYTES, F64, check, lib
+from ._lib import DIGEST_BYTES, ELEM_BYTES, F64, check, lib
 from .matrix import GENERATOR_INTERNAL
 from .merkle import MerkleTree, _DigestPlan, _DigestTable, _prove_batch
 
@@ -60,8 +60,8 @@ def commit_layer(field, hash_id, evaluations, folding_factor):
     n = e.shape[0]
     rows = n // folding_factor
     tr = np.empty_like(e)
-    leaves = np.empty((max(rows, 1), 32), dtype=np.uint8)
-    nodes = np.empty((max(rows, 1), 32), dtype=np.uint8)
+    leaves = np.empty((max(rows, 1), DIGEST_BYTES[hash_id]), dtype=np.uint8)
+    nodes = np.empty((max(rows, 1), DIGEST_BYTES[hash_id]), dtype=np.uint8)
     check(lib().wg_fri_commit_layer(field, hash_id, C.c_void_p(e.ctypes.data), n, folding_factor, C.c_void_p(tr.ctypes.data),
                                     C.c_void_p(leaves.ctypes.data), C.c_void_p(nodes.ctypes.data)))
     shape = (rows, folding_factor) if field == F64 else (rows, folding_factor, 2)
@@ -149,8 +149,8 @@ class FriProver:
         rows = n // N
         s = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         tr = torch.empty((rows, N, w), dtype=torch.int64, device=self.device)
-        leaves = torch.empty((max(rows, 1), 32), dtype=torch.uint8, device=self.device)
-        nodes = torch.empty((max(rows, 1), 32), dtype=torch.uint8, device=self.device)
+        leaves = torch.empty((max(rows, 1), DIGEST_BYTES[self.hash_id]), dtype=torch.uint8, device=self.device)
+        nodes = torch.empty((max(rows, 1), DIGEST_BYTES[self.hash_id]), dtype=torch.uint8, device=self.device)
         check(lib().wg_fri_commit_layer_dev(self.field, self.hash_id, C.c_void_p(ev.data_ptr()), n, N, C.c_void_p(tr.data_ptr()),
                                             C.c_void_p(leaves.data_ptr()), C.c_void_p(nodes.data_ptr()), s))
         layer = FriLayer(self.hash_id, tr, leaves, nodes, N)
@@ -172,7 +172,7 @@ class FriProver:
             fft.interpolate_poly_with_offset(self.field, e, fft.get_inv_twiddles(self.field, n), self.domain_offset())
         size = n // self.options.blowup_factor
         rem = np.ascontiguousarray(e[:size])
-        digest = np.empty((1, 32), dtype=np.uint8)
+        digest = np.empty((1, DIGEST_BYTES[self.hash_id]), dtype=np.uint8)
         check(lib().wg_hash_rows(self.field, self.hash_id, C.c_void_p(rem.ctypes.data), 1, size, size, C.c_void_p(digest.ctypes.data)))
         self.remainder_commitment = bytes(digest[0])
         channel.commit_fri_layer(self.remainder_commitment)
@@ -198,7 +198,7 @@ class FriProver:
                 li = torch.tensor(plan.leaf_idx, dtype=torch.int64, device=self.device)
                 ni = torch.tensor(plan.node_idx, dtype=torch.int64, device=self.device)
                 lv = layer.leaves[li].cpu().numpy()
-                nv = layer.nodes[ni].cpu().numpy() if plan.node_idx else np.empty((0, 32), dtype=np.uint8)
+                nv = layer.nodes[ni].cpu().numpy() if plan.node_idx else np.empty((0, DIGEST_BYTES[self.hash_id]), dtype=np.uint8)
                 proof = _prove_batch(_DigestTable(plan.leaf_idx, lv, plan.node_idx, nv), n_leaves, depth, positions)
                 pi = torch.tensor(positions, dtype=torch.int64, device=self.device)
                 vals = layer.evaluations[pi].cpu().numpy().view(np.uint64)

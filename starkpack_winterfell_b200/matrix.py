@@ -5,7 +5,7 @@ import ctypes as C
 import numpy as np
 
 from . import fft
-from ._lib import F64, F128, check, lib
+from ._lib import DIGEST_BYTES, F64, F128, check, lib
 from .merkle import MerkleTree
 
 GENERATOR_INTERNAL = {  # GENERATOR in internal representation: f64 Montgomery word of 7; f128 canonical 3
@@ -118,7 +118,7 @@ class RowMatrix:
         return self.data[i, : self.elements_per_row]
 
     def hash_rows(self, hash_id):
-        leaves = np.empty((self.num_rows(), 32), dtype=np.uint8)
+        leaves = np.empty((self.num_rows(), DIGEST_BYTES[hash_id]), dtype=np.uint8)
         check(lib().wg_hash_rows(self.field, hash_id, C.c_void_p(self.data.ctypes.data), self.num_rows(), self.row_width,
                                  self.elements_per_row, C.c_void_p(leaves.ctypes.data)))
         return leaves
@@ -137,6 +137,6 @@ class RowMatrix:
         ptrs = (C.c_void_p * k)(*[m.data.ctypes.data for m in traces_lde])
         rws = (C.c_uint64 * k)(*[m.row_width for m in traces_lde])
         els = (C.c_uint64 * k)(*[m.elements_per_row for m in traces_lde])
-        leaves = np.empty((rows, 32), dtype=np.uint8)
+        leaves = np.empty((rows, DIGEST_BYTES[hash_id]), dtype=np.uint8)
         check(lib().wg_hash_comb_rows(self.field, hash_id, k, ptrs, rws, els, rows, C.c_void_p(leaves.ctypes.data)))
         return MerkleTree.new(hash_id, leaves)

@@ -4,7 +4,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import F64, F128, check, lib
+from ._lib import DIGEST_BYTES, F64, F128, check, lib
 from .matrix import ColMatrix, RowMatrix, StarkDomain, _ptr_array
 from .merkle import MerkleTree, MerkleTreeError, _DigestPlan, _DigestTable, _prove, _prove_batch
 
@@ -139,9 +139,9 @@ def build_trace_commitment(hash_id, traces, domain, want_lde=True, want_polys=Tr
         for t in traces:
             rw = (t.num_cols() * deg + 7) // 8 * 8
             ldes.append(np.empty((L, rw) if f == F64 else (L, rw, 2), dtype=np.uint64))
-    leaves = np.empty((L, 32), dtype=np.uint8)
-    nodes = np.empty((L, 32), dtype=np.uint8)
-    root = np.empty(32, dtype=np.uint8)
+    leaves = np.empty((L, DIGEST_BYTES[hash_id]), dtype=np.uint8)
+    nodes = np.empty((L, DIGEST_BYTES[hash_id]), dtype=np.uint8)
+    root = np.empty(DIGEST_BYTES[hash_id], dtype=np.uint8)
     args = (n, B, len(traces), cpt, _ptr_array(cols),
             _ptr_array([c for p in polys for c in p]) if polys else None,
             _ptr_array(ldes) if ldes else None,
@@ -165,9 +165,9 @@ def build_constraint_commitment(hash_id, composition_poly, domain):
     L = n * B
     rw = (composition_poly.num_cols() + 7) // 8 * 8
     lde = np.empty((L, rw) if f == F64 else (L, rw, 2), dtype=np.uint64)
-    leaves = np.empty((L, 32), dtype=np.uint8)
-    nodes = np.empty((L, 32), dtype=np.uint8)
-    root = np.empty(32, dtype=np.uint8)
+    leaves = np.empty((L, DIGEST_BYTES[hash_id]), dtype=np.uint8)
+    nodes = np.empty((L, DIGEST_BYTES[hash_id]), dtype=np.uint8)
+    root = np.empty(DIGEST_BYTES[hash_id], dtype=np.uint8)
     check(lib().wg_commit_polys(f, hash_id, n, B, composition_poly.num_cols(), _ptr_array(composition_poly.columns),
                                 C.c_void_p(lde.ctypes.data), C.c_void_p(leaves.ctypes.data), C.c_void_p(nodes.ctypes.data),
                                 C.c_void_p(root.ctypes.data)))
@@ -208,7 +208,7 @@ class ResidentCommitment:
             polys = polys_out
         elif want_polys:
             polys = [[np.empty_like(c) for c in t.columns] for t in traces]
-        root = np.empty(32, dtype=np.uint8)
+        root = np.empty(DIGEST_BYTES[hash_id], dtype=np.uint8)
         h = C.c_void_p()
         check(lib().wg_commitment_from_trace(f, hash_id, n, domain.blowup, len(traces), cpt, _ptr_array(cols),
                                              _ptr_array([c for p in polys for c in p]) if polys else None,
@@ -218,7 +218,7 @@ class ResidentCommitment:
     @classmethod
     def from_polys(cls, hash_id, composition_poly, domain):
         f = composition_poly.field
-        root = np.empty(32, dtype=np.uint8)
+        root = np.empty(DIGEST_BYTES[hash_id], dtype=np.uint8)
         h = C.c_void_p()
         check(lib().wg_commitment_from_polys(f, hash_id, composition_poly.num_rows(), domain.blowup, composition_poly.num_cols(),
                                              _ptr_array(composition_poly.columns), C.c_void_p(root.ctypes.data), C.byref(h)))
@@ -240,7 +240,7 @@ class ResidentCommitment:
 
     def _digests(self, which, idx):
         idx = np.ascontiguousarray(idx, dtype=np.uint64)
-        out = np.empty((len(idx), 32), dtype=np.uint8)
+        out = np.empty((len(idx), DIGEST_BYTES[self.hash_id]), dtype=np.uint8)
         if len(idx):
             check(lib().wg_commitment_digests(self._h, which, len(idx), C.c_void_p(idx.ctypes.data), C.c_void_p(out.ctypes.data)))
         return out
@@ -269,8 +269,8 @@ class ResidentCommitment:
         if want_lde:
             for rw in self.row_widths:
                 ldes.append(np.empty((L, rw) if self.field == F64 else (L, rw, 2), dtype=np.uint64))
-        leaves = np.empty((L, 32), dtype=np.uint8)
-        nodes = np.empty((L, 32), dtype=np.uint8)
+        leaves = np.empty((L, DIGEST_BYTES[self.hash_id]), dtype=np.uint8)
+        nodes = np.empty((L, DIGEST_BYTES[self.hash_id]), dtype=np.uint8)
         check(lib().wg_commitment_download(self._h, _ptr_array(ldes) if ldes else None, C.c_void_p(leaves.ctypes.data),
                                            C.c_void_p(nodes.ctypes.data)))
         mats = [RowMatrix(self.field, d, d.shape[1], c) for d, c in zip(ldes, self.cols_per_trace)]
