@@ -200,6 +200,18 @@ uint64_t wg_lde_scratch_elems(int field, uint32_t n_cols, uint64_t n, uint64_t b
 
 int wg_interpolate_columns_dev(int field, const void* d_cols, uint32_t n_cols, uint64_t n, void* d_polys, void* d_scratch,
                                uint64_t scratch_elems, void* stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same result as
+ * wg_interpolate_columns_dev, but the two-pass NTT's intermediate lives in a file-scope static __device__ array of
+ * WG_NOALLOC_SCRATCH_BYTES (16 MiB, held by every GPU that loads the library until exit) instead of a caller buffer, and
+ * the call performs NO device or host allocation: n_cols * n elements must fit in that array (2^21 f64 / 2^20 f128
+ * elements, e.g. 8 columns x 2^18 rows), larger requests return WG_ERR_TOO_LARGE; the cached twiddle tables of length n
+ * must already be resident (any earlier wg_interpolate_columns_dev of that length builds them), else WG_ERR_ARG. Every
+ * call shares the one array, which keeps the previous call's contents (each call overwrites all it reads, nothing needs
+ * clearing): calls that overlap on the GPU (different streams / threads) race. */
+#define WG_NOALLOC_SCRATCH_BYTES (16u << 20)
+int wg_interpolate_columns_noalloc_dev(int field, const void* d_cols, uint32_t n_cols, uint64_t n, void* d_polys, void* stream);
+
 /* d_lde row-major (n*blowup) x row_width; columns n_cols..row_width-1 are written as zero. A smaller scratch
  * than wg_lde_scratch_elems makes the call run in column chunks (minimum: 8 columns' worth). */
 int wg_lde_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset_host,

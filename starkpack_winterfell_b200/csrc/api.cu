@@ -145,6 +145,16 @@ struct Tables {
     return WG_OK;
   }
 
+  // lookup only (never builds, never allocates): are the tables of a length-2^log_n inverse two-pass transform resident?
+  bool have_tws(int log_s, bool inv) {
+    std::lock_guard<std::mutex> lk(mu);
+    return tws.find(std::make_pair(log_s, (int)inv)) != tws.end();
+  }
+  bool have_tm(int log_n, bool inv) {
+    std::lock_guard<std::mutex> lk(mu);
+    return tm.find(std::make_pair(log_n, (int)inv)) != tm.end();
+  }
+
   // two-level power table of `base`: lo[e] = scale*base^e (e < 2^lb), hi[h] = base^(h << lb) (h < 2^(log_n-lb))
   static void fill_two(T base, T scale, int log_n, int lb, T* lo, T* hi) {
     T acc = scale;
@@ -1560,6 +1570,57 @@ static int h_fri_apply_drp(const void* transposed, uint64_t rows, uint32_t ff, c
   return WG_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// Scratch of wg_interpolate_columns_noalloc_dev: a file-scope device array instead of a caller / cudaMalloc buffer. Every
+// GPU that loads the library holds these 16 MiB until exit. In HOST code the name below is only a stand-in for the symbol,
+// not a device address: the address is fetched once (per process = per device, the library is bound to one device) with
+// cudaGetSymbolAddress while that device is current, and only that pointer is handed to kernels.
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)WG_NOALLOC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+static void* g_noalloc_ptr = nullptr;
+static int g_noalloc_dev = -1;
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch(void** out) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  int dev = -1;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (!g_noalloc_ptr || g_noalloc_dev != dev) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) return fail(WG_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch): %s", cudaGetErrorString(e));
+    g_noalloc_ptr = p;
+    g_noalloc_dev = dev;
+  }
+  *out = g_noalloc_ptr;
+  return WG_OK;
+}
+
+template <class F>
+static int interpolate_columns_noalloc(const typename F::T* d_in, uint32_t n_cols, uint64_t n, typename F::T* d_out, cudaStream_t stream) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, 1));
+  if (n_cols == 0) return WG_OK;
+  const uint64_t max_elems = NOALLOC_SCRATCH_BYTES / sizeof(T);
+  if ((uint64_t)n_cols * n > max_elems)
+    return fail(WG_ERR_TOO_LARGE, "no-allocation interpolation holds at most %llu elements (%zu bytes of static scratch); asked for %u x %llu",
+                (unsigned long long)max_elems, NOALLOC_SCRATCH_BYTES, n_cols, (unsigned long long)n);
+  // the twiddle tables are cached device allocations built on first use of a length by the ordinary entry points; this
+  // entry point only looks them up
+  const int log_n = ilog2(n);
+  int na, nb;
+  split_passes(log_n, &na, &nb);
+  Tables<F>& tb = tables<F>();
+  const bool ok = tb.have_tws(nb, true) && (na == 0 || (tb.have_tws(na, true) && tb.have_tm(log_n, true)));
+  if (!ok)
+    return fail(WG_ERR_ARG, "twiddle tables for length 2^%d are not resident: run wg_interpolate_columns_dev once with this length "
+                "outside the no-allocation region", log_n);
+  void* scr = nullptr;
+  WG_TRY(noalloc_scratch(&scr));
+  // pass A writes every one of the n_cols*n scratch elements before pass B reads them: nothing has to start at zero
+  return interpolate_columns_dev<F>(d_in, n_cols, n, d_out, (T*)scr, max_elems, stream);
+}
+
 }  // namespace wg
 
 #include "dist.cuh"
@@ -1862,6 +1923,14 @@ int wg_interpolate_columns_dev(int field, const void* d_cols, uint32_t n_cols, u
   WG_FIELD_DISPATCH(field,
                     interpolate_columns_dev<Gl64>((const uint64_t*)d_cols, n_cols, n, (uint64_t*)d_polys, (uint64_t*)d_scratch, scratch_elems, s),
                     interpolate_columns_dev<F128>((const u128*)d_cols, n_cols, n, (u128*)d_polys, (u128*)d_scratch, scratch_elems, s));
+}
+
+int wg_interpolate_columns_noalloc_dev(int field, const void* d_cols, uint32_t n_cols, uint64_t n, void* d_polys, void* stream) {
+  if (!d_cols || !d_polys) return fail(WG_ERR_ARG, "null pointer");
+  WG_TRY(ensure_device());
+  cudaStream_t s = (cudaStream_t)stream;
+  WG_FIELD_DISPATCH(field, interpolate_columns_noalloc<Gl64>((const uint64_t*)d_cols, n_cols, n, (uint64_t*)d_polys, s),
+                    interpolate_columns_noalloc<F128>((const u128*)d_cols, n_cols, n, (u128*)d_polys, s));
 }
 
 int wg_lde_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, const void* offset_host,
