@@ -38,6 +38,8 @@ def col_matrices(wg, field, traces):
     (F128, B3, [2, 2, 2, 2], 1024, 8),
     (F128, SHA3, [4], 1 << 13, 8),
     (F64, B3, [100], 1 << 14, 8),
+    (F64, 2, [13], 4096, 8),          # Blake3_192: 24-byte digests through leaves, nodes, proofs
+    (F128, 2, [2, 2], 1024, 8),
 ])
 def test_resident_commitment_query(wg, oracle, field, h, shapes, n, blowup):
     traces = [rand_cols(field, 700 + 7 * i + c, c, n) for i, c in enumerate(shapes)]
