@@ -302,7 +302,8 @@ int wg_sharded_commit(int field, int hash, uint64_t n_rows, uint64_t blowup, uin
                       const void* const* local_column_ptrs, void* const* local_polys_out, int exchange, uint32_t chunks,
                       uint8_t* root_out, void** handle);
 /* shape of the handle: global LDE rows, first row / number of rows held here, received column blocks (global column
- * order) with their real columns and stored row widths (arrays of WG_SHARD_MAX_BLOCKS), exchange form and chunks used */
+ * order) with their real columns and stored row widths (arrays of WG_SHARD_MAX_BLOCKS; an exchanged block is stored without
+ * pad columns: width = columns), exchange form and chunks used */
 int wg_sharded_info(const void* handle, uint64_t* lde_rows, uint64_t* row_start, uint64_t* row_count, uint32_t* n_blocks,
                     uint32_t* block_cols, uint32_t* block_row_widths, int* exchange, uint32_t* chunks);
 /* milliseconds on the commit's stream (CUDA events): 0 interpolate, 1 LDE (exchange of earlier chunks runs underneath),

@@ -37,12 +37,14 @@ static inline void shard_plan(uint32_t total_cols, uint32_t world, int exchange,
   } else if (ex == WG_EXCHANGE_AUTO) {
     // narrow shards (a StarkPack trace per GPU) finish their last LDE pass in a few milliseconds and the fused stores
     // save the whole all-to-all; wider shards would be NVLink-bound at 32-byte stores and pipeline NCCL instead
-    if (per_rank <= 16 && world <= (uint32_t)PassArgs<Gl64>::MAX_PEERS) ex = WG_EXCHANGE_FUSED_P2P;
+    // (measured, profiles/r2_forms_*gpu.jsonl: 25 f64 columns per rank on 4 GPUs: fused 43.3 ms, pipelined x4 29.4 ms;
+    //  2 - 8 f128 columns per rank, cfg4: fused 3.9 / 7.1 ms against 5.8 / 8.3 ms)
+    if (per_rank <= 8 && world <= (uint32_t)PassArgs<Gl64>::MAX_PEERS) ex = WG_EXCHANGE_FUSED_P2P;
     else ex = WG_EXCHANGE_PIPELINED;
   }
   if (ex == WG_EXCHANGE_FUSED_P2P || ex == WG_EXCHANGE_ALLTOALL) k = 1;
   if (ex == WG_EXCHANGE_PIPELINED) {
-    if (k == 0) k = per_rank >= 64 ? 4 : (per_rank >= 16 ? 2 : 1);
+    if (k == 0) k = per_rank >= 25 ? 4 : (per_rank + 7) / 8;  // 8-column chunks, at most 4: the last chunk's exchange is the exposed one
     const uint32_t max_k = (per_rank + 7) / 8;  // at least 8 columns per chunk
     if (k > max_k) k = max_k;
     while (k > 1 && world * k > WG_SHARD_MAX_BLOCKS) k--;
@@ -54,6 +56,10 @@ static inline void shard_plan(uint32_t total_cols, uint32_t world, int exchange,
   *ex_out = ex;
   *k_out = k ? k : 1;
 }
+// stored row width of an exchanged column block: exactly its columns. The single-GPU LDE pads rows to a multiple of 8
+// columns because the reference's RowMatrix does (row_matrix.rs:110-133); pad columns are never hashed, and here they
+// would only be bytes on NVLink (13 columns per rank at 8 GPUs: 16 stored = +23 %).
+static inline uint64_t shard_rw(uint32_t cols) { return cols; }
 // heap index of the global tree (n_leaves leaves, `world` subtrees) -> owner. Levels above the subtree roots (index <
 // world) live in the top array; node i at level m = 2^floor(log2 i) >= world belongs to rank (i - m) / (m / world) with
 // local heap index m/world + (i - m) % (m / world).
@@ -186,7 +192,7 @@ static void shard_layout(ShardedCommit* h) {
       shard_chunk(c, h->K, k, &cs, &cc);
       ShardBlock b;
       b.cols = cc;
-      b.rw = (uint64_t)(cc + 7) / 8 * 8;
+      b.rw = shard_rw(cc);
       b.off = off;
       off += (size_t)h->rows * b.rw;
       h->blocks.push_back(b);
@@ -258,7 +264,7 @@ static int shard_scratch_alloc(const ShardedCommit* h, uint32_t my_cols, bool ne
   s->scr_bytes = se * sizeof(T) + 16;
   WG_TRY(cached_malloc(&s->scr, s->scr_bytes));
   if (need_send) {
-    s->send_bytes = (size_t)h->L * ((uint64_t)(maxc + 7) / 8 * 8) * sizeof(T);
+    s->send_bytes = (size_t)h->L * shard_rw(maxc) * sizeof(T);
     if (s->send_bytes == 0) s->send_bytes = 16;
     WG_TRY(cached_malloc(&s->send[0], s->send_bytes));
     if (h->K > 1) WG_TRY(cached_malloc(&s->send[1], s->send_bytes));
@@ -363,7 +369,7 @@ static int sharded_commit_run(ShardedCommit* h, const typename F::T* d_cols, typ
     for (uint32_t k = 0; k < h->K && rc == WG_OK; k++) {
       uint32_t cs, cc;
       shard_chunk(my_cols, h->K, k, &cs, &cc);
-      const uint64_t rw_k = (uint64_t)(cc + 7) / 8 * 8;
+      const uint64_t rw_k = shard_rw(cc);
       T* send = (T*)ss.send[k & 1];
       if (k >= 2) {  // the exchange that last read this send buffer must be over
         if (cudaStreamWaitEvent(sc, ev_x[k & 1], 0) != cudaSuccess) rc = fail(WG_ERR_CUDA, "cudaStreamWaitEvent");
@@ -530,7 +536,7 @@ static int sharded_emulate(int hash, uint64_t n, uint64_t blowup, uint32_t total
         uint32_t cs, cc;
         shard_chunk(c, K, k, &cs, &cc);
         if (!cc) continue;
-        const uint64_t rw_k = (uint64_t)(cc + 7) / 8 * 8;
+        const uint64_t rw_k = shard_rw(cc);
         T* send = (T*)ss.send[k & 1];
         WG_TRY(lde_dev<F>(polys + (size_t)cs * n, cc, n, blowup, offset, send, rw_k, (T*)ss.scr, ss.scr_elems, sc));
         for (uint32_t o = 0; o < G; o++) {  // what ncclSend(o) / ncclRecv(r) on rank o would move

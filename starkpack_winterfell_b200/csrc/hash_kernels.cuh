@@ -59,11 +59,14 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
   }
   bool sha_done = false;
 
+  uint32_t t_base = 0;  // matrix that holds unit u0: advances monotonically with the slabs (no per-element search from 0)
   // an empty row still takes one (padding-only) block: the digest of the empty input
   for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done) || (IS_B3 && nbytes == 0 && u0 == 0);
        u0 += SU) {
     // ---- stage SU units of each of the warp's 32 rows: issue all SU loads first (one long-scoreboard wait per
     // slab instead of one per element), then convert and store
+    if (A.n_traces > 1)
+      while (t_base + 1 < A.n_traces && u0 >= A.unit_off[t_base + 1]) t_base++;
     uint64_t vals[SU];
 #pragma unroll
     for (int it = 0; it < SU; it++) {
@@ -73,7 +76,7 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
       const uint64_t row = row0 + r;
       uint64_t v = 0;
       if (gu < units_total && row < A.rows) {
-        uint32_t t = 0;
+        uint32_t t = t_base;
         if (A.n_traces > 1)
           while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
         const uint32_t lu = gu - A.unit_off[t];
