@@ -270,9 +270,12 @@ int wg_lde_scatter_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t
  *                          all-to-all runs on its own stream under chunk k+1's LDE;
  *   WG_EXCHANGE_FUSED_P2P  the LDE's last pass stores each row straight into its owner's receive buffer through
  *                          peer-mapped pointers (CUDA IPC, NVLink P2P stores): no send buffer, no all-to-all;
- *   WG_EXCHANGE_AUTO       fused up to 16 columns per rank (G <= 8), pipelined otherwise (plain when one chunk). */
+ *   WG_EXCHANGE_P2P_COPY   chunked like PIPELINED, but every rank PUSHES its slices into the owners' receive buffers
+ *                          (peer-mapped with CUDA IPC) with cudaMemcpyAsync: copy engines over NVLink, no SM used by the
+ *                          exchange, one 4-byte NCCL all-gather as the barrier behind the copies (single node);
+ *   WG_EXCHANGE_AUTO       fused up to 8 columns per rank (G <= 8), P2P_COPY in 8-column chunks (at most 4) otherwise. */
 #define WG_DIST_ID_BYTES 128
-enum { WG_EXCHANGE_AUTO = 0, WG_EXCHANGE_ALLTOALL = 1, WG_EXCHANGE_PIPELINED = 2, WG_EXCHANGE_FUSED_P2P = 3 };
+enum { WG_EXCHANGE_AUTO = 0, WG_EXCHANGE_ALLTOALL = 1, WG_EXCHANGE_PIPELINED = 2, WG_EXCHANGE_FUSED_P2P = 3, WG_EXCHANGE_P2P_COPY = 4 };
 #define WG_SHARD_MAX_BLOCKS 64 /* received column blocks (ranks x chunks) the leaf kernel concatenates */
 
 int wg_dist_unique_id(uint8_t* id_out /* WG_DIST_ID_BYTES */);

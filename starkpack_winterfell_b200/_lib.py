@@ -138,8 +138,8 @@ def init(device=0):
     check(lib().wg_init(device))
 
 
-EXCHANGE_AUTO, EXCHANGE_ALLTOALL, EXCHANGE_PIPELINED, EXCHANGE_FUSED_P2P = 0, 1, 2, 3
-EXCHANGE_NAMES = {0: "auto", 1: "alltoall", 2: "pipelined", 3: "fused_p2p"}
+EXCHANGE_AUTO, EXCHANGE_ALLTOALL, EXCHANGE_PIPELINED, EXCHANGE_FUSED_P2P, EXCHANGE_P2P_COPY = 0, 1, 2, 3, 4
+EXCHANGE_NAMES = {0: "auto", 1: "alltoall", 2: "pipelined", 3: "fused_p2p", 4: "p2p_copy"}
 DIST_ID_BYTES = 128
 SHARD_MAX_BLOCKS = 64
 

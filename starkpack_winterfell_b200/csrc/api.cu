@@ -2207,7 +2207,7 @@ int wg_shard_chunks(uint32_t cols, uint32_t k, uint32_t idx, uint32_t* start, ui
 }
 int wg_shard_plan(uint32_t total_cols, uint32_t world, int exchange, uint32_t chunks, int* exchange_out, uint32_t* chunks_out) {
   if (!exchange_out || !chunks_out || world == 0) return fail(WG_ERR_ARG, "bad plan query");
-  if (exchange < WG_EXCHANGE_AUTO || exchange > WG_EXCHANGE_FUSED_P2P) return fail(WG_ERR_ARG, "unknown exchange form %d", exchange);
+  if (exchange < WG_EXCHANGE_AUTO || exchange > WG_EXCHANGE_P2P_COPY) return fail(WG_ERR_ARG, "unknown exchange form %d", exchange);
   if (exchange == WG_EXCHANGE_FUSED_P2P && world > (uint32_t)PassArgs<Gl64>::MAX_PEERS)
     return fail(WG_ERR_UNSUPPORTED, "fused exchange supports at most %d ranks", PassArgs<Gl64>::MAX_PEERS);
   shard_plan(total_cols, world, exchange, chunks, exchange_out, chunks_out);

@@ -39,18 +39,20 @@ static inline void shard_plan(uint32_t total_cols, uint32_t world, int exchange,
     // save the whole all-to-all; wider shards would be NVLink-bound at 32-byte stores and pipeline NCCL instead
     // (measured, profiles/r2_forms_*gpu.jsonl: 25 f64 columns per rank on 4 GPUs: fused 43.3 ms, pipelined x4 29.4 ms;
     //  2 - 8 f128 columns per rank, cfg4: fused 3.9 / 7.1 ms against 5.8 / 8.3 ms)
+    //  13 f64 columns per rank on 8 GPUs: NCCL send/recv moves ~350 GB/s per GPU and its kernels share the SMs with the LDE,
+    //  copy-engine pushes into the peers' mapped buffers leave the SMs alone: WG_EXCHANGE_P2P_COPY is the wide-shard default)
     if (per_rank <= 8 && world <= (uint32_t)PassArgs<Gl64>::MAX_PEERS) ex = WG_EXCHANGE_FUSED_P2P;
-    else ex = WG_EXCHANGE_PIPELINED;
+    else ex = WG_EXCHANGE_P2P_COPY;
   }
   if (ex == WG_EXCHANGE_FUSED_P2P || ex == WG_EXCHANGE_ALLTOALL) k = 1;
-  if (ex == WG_EXCHANGE_PIPELINED) {
+  if (ex == WG_EXCHANGE_PIPELINED || ex == WG_EXCHANGE_P2P_COPY) {
     if (k == 0) k = per_rank >= 25 ? 4 : (per_rank + 7) / 8;  // 8-column chunks, at most 4: the last chunk's exchange is the exposed one
     const uint32_t max_k = (per_rank + 7) / 8;  // at least 8 columns per chunk
     if (k > max_k) k = max_k;
     while (k > 1 && world * k > WG_SHARD_MAX_BLOCKS) k--;
     if (k <= 1) {
       k = 1;
-      ex = WG_EXCHANGE_ALLTOALL;
+      if (ex == WG_EXCHANGE_PIPELINED) ex = WG_EXCHANGE_ALLTOALL;
     }
   }
   *ex_out = ex;
@@ -327,7 +329,8 @@ static int sharded_commit_run(ShardedCommit* h, const typename F::T* d_cols, typ
   WG_TRY(shard_alloc_outputs(h, d_polys == nullptr, my_cols));
   T* polys = d_polys ? d_polys : (T*)h->polys;
   const bool fused = h->exchange == WG_EXCHANGE_FUSED_P2P && G > 1;
-  if (fused) {
+  const bool p2pcopy = h->exchange == WG_EXCHANGE_P2P_COPY && G > 1;
+  if (fused || p2pcopy) {
     WG_TRY(peer_buf_acquire(h->recv_bytes, &h->peer_slot));
     h->recv = g_dist.peer_bufs[h->peer_slot].ptr;
   } else {
@@ -378,6 +381,21 @@ static int sharded_commit_run(ShardedCommit* h, const typename F::T* d_cols, typ
       if (rc != WG_OK) break;
       cudaEventRecord(ev_lde, sc);
       cudaStreamWaitEvent(sx, ev_lde, 0);
+      if (p2pcopy) {
+        // push my slice of every owner's row block into ITS receive buffer (peer-mapped, CUDA IPC) with the copy engines:
+        // each slice is contiguous on both sides; owners are visited round-robin from my right-hand neighbour
+        const size_t bytes = (size_t)h->rows * rw_k * sizeof(T);
+        const ShardBlock& mine_k = h->blocks[(size_t)r * h->K + k];
+        for (uint32_t i = 0; i < G && cc && rc == WG_OK; i++) {
+          const uint32_t o = (r + 1 + i) % G;
+          T* dst = (T*)g_dist.peer_bufs[h->peer_slot].peers[o] + mine_k.off;
+          if (cudaMemcpyAsync(dst, send + (size_t)o * h->rows * rw_k, bytes, cudaMemcpyDeviceToDevice, sx) != cudaSuccess)
+            rc = fail(WG_ERR_CUDA, "peer copy of chunk %u to rank %u: %s", k, o, cudaGetErrorString(cudaGetLastError()));
+          if (o != r) h->bytes_sent += bytes;
+        }
+        cudaEventRecord(ev_x[k & 1], sx);
+        continue;
+      }
       ncclResult_t nr = g_nccl.GroupStart();
       for (uint32_t g = 0; g < G && nr == ncclSuccess; g++) {
         const ShardBlock& from_g = h->blocks[(size_t)g * h->K + k];
@@ -393,6 +411,13 @@ static int sharded_commit_run(ShardedCommit* h, const typename F::T* d_cols, typ
       cudaEventRecord(ev_x[k & 1], sx);
     }
     CUDA_TRY(cudaEventRecord(h->ev[2], sc));
+    if (rc == WG_OK && p2pcopy) {
+      // every rank's pushes have landed once every rank's copies are complete: a stream-ordered barrier behind them
+      uint8_t* tok = g_dist.d_small + 64 * (PassArgs<Gl64>::MAX_PEERS + 1);
+      ncclResult_t nr = g_nccl.AllGather(tok + 64 * G, tok, 4, ncclUint8, g_dist.comm, sx);
+      if (nr != ncclSuccess) rc = fail(WG_ERR_CUDA, "NCCL barrier after the peer copies: %s", g_nccl.GetErrorString(nr));
+      cudaEventRecord(ev_x[(h->K - 1) & 1], sx);
+    }
     if (rc == WG_OK) {
       cudaStreamWaitEvent(sc, ev_x[0], 0);
       if (h->K > 1) cudaStreamWaitEvent(sc, ev_x[1], 0);

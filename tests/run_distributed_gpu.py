@@ -47,7 +47,7 @@ def small_shapes(dev):
         want = oracle.commit_trace(field, hash_id, [full], blowup, want=("leaves", "nodes", "lde")) if rank == 0 else None
         s0, cnt = sharded.shard_columns(total_cols, world, rank)
         cols = _to_dev(full[s0: s0 + cnt], field, dev)
-        for exchange, chunks in ((1, 0), (2, 2), (2, 4), (3, 0), (0, 0)):
+        for exchange, chunks in ((1, 0), (2, 2), (2, 4), (3, 0), (4, 1), (4, 3), (0, 0)):
             if exchange == 3 and world > 8:
                 continue
             roots = []

@@ -71,9 +71,11 @@ def test_shard_partition_helpers_host_only():
         assert sum(c for _, c in got) == cols and all(c % 8 == 0 for _, c in got[:-1] if c and got[-1][1])
     # auto plan: fused for narrow shards on <= 8 ranks, pipelined otherwise, never more than 64 received blocks
     assert sharded.shard_plan(16, 8) == (_lib.EXCHANGE_FUSED_P2P, 1)
-    assert sharded.shard_plan(100, 2) == (_lib.EXCHANGE_PIPELINED, 4)
-    assert sharded.shard_plan(100, 8) == (_lib.EXCHANGE_PIPELINED, 2)
-    assert sharded.shard_plan(256, 8) == (_lib.EXCHANGE_PIPELINED, 4)
+    assert sharded.shard_plan(100, 2) == (_lib.EXCHANGE_P2P_COPY, 4)
+    assert sharded.shard_plan(100, 8) == (_lib.EXCHANGE_P2P_COPY, 2)
+    assert sharded.shard_plan(256, 8) == (_lib.EXCHANGE_P2P_COPY, 4)
+    assert sharded.shard_plan(100, 8, _lib.EXCHANGE_PIPELINED) == (_lib.EXCHANGE_PIPELINED, 2)
+    assert sharded.shard_plan(9, 1, _lib.EXCHANGE_P2P_COPY) == (_lib.EXCHANGE_ALLTOALL, 1)
     assert sharded.shard_plan(100, 1) == (_lib.EXCHANGE_ALLTOALL, 1)
     ex, k = sharded.shard_plan(4096, 32, _lib.EXCHANGE_PIPELINED, 8)
     assert 32 * k <= _lib.SHARD_MAX_BLOCKS

@@ -25,7 +25,7 @@ CASES = [
 
 
 @pytest.mark.parametrize("G,field,hash_id,n,blowup,total_cols", CASES)
-@pytest.mark.parametrize("exchange,chunks", [(1, 0), (2, 2), (2, 4), (3, 0), (0, 0)])
+@pytest.mark.parametrize("exchange,chunks", [(1, 0), (2, 2), (2, 4), (3, 0), (4, 2), (0, 0)])
 def test_emulated_sharded_commit_matches_oracle(oracle, G, field, hash_id, n, blowup, total_cols, exchange, chunks):
     from starkpack_winterfell_b200 import _lib, sharded
 
