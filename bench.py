@@ -126,7 +126,7 @@ def host_threads():
 
 
 def pick_cpu_log_rows(requested):
-    """Full 2^22 rows when the host can do it in bounded time (>= 24 threads, >= 96 GB free: ~45 GB working set),
+    """Full 2^22 rows when the host can do it in bounded time (>= 16 threads, >= 96 GB free: ~60 GB working set, 50 - 80 s),
     otherwise a 2^20-row sample scaled linearly in rows."""
     if requested:
         return requested
@@ -136,7 +136,7 @@ def pick_cpu_log_rows(requested):
         free = psutil.virtual_memory().available
     except Exception:
         free = 0
-    return LOG_ROWS if (host_threads() >= 24 and free > 96e9) else 20
+    return LOG_ROWS if (host_threads() >= 16 and free > 96e9) else 20
 
 
 def cpu_commit_sample(log_rows_sample, runs=1):
@@ -582,7 +582,10 @@ def run_ours(args):
     kbytes_launch = L * my_cols * 8 / dom_launches
     kio_launch = 2 * kbytes_launch
     achieved = kbytes_launch / (dom_ms * 1e-3) / 1e9
-    traffic, traffic_src = None, None
+    # cited constants from one ncu pass at this size (profiles/r2_traffic.json names the commit they were taken at): DRAM
+    # bytes and executed warp-instructions per launch. int_issue_frac = those instructions / the kernel time measured in
+    # THIS run / the measured integer peak (1.0 warp-instruction per clock per SMSP, profiles/r2_int_peak_summary.md).
+    traffic, traffic_src, int_issue = None, None, None
     try:
         with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             tj = json.load(f)
@@ -590,6 +593,16 @@ def run_ours(args):
             traffic = tj["phases"][dom]["dram_bytes"]
             traffic_src = ("cited constant: ncu dram__bytes_read.sum + dram__bytes_write.sum of one launch at this size, captured at "
                            f"commit {tj.get('commit', '?')} (profiles/r2_traffic.json); not re-measured in this run")
+            ipeak = float(tj.get("int_peak_warp_inst_per_s", 592 * 1.965e9))
+            int_issue = {"peak_warp_inst_per_s": ipeak, "peak_source": "profiles/r2_int_peak_summary.md (measured: ALU pipe 0.5 + FMA pipe 0.5 "
+                         "warp-instructions per clock per SMSP at 1965 MHz)", "instructions_source": traffic_src.replace(
+                             "dram__bytes_read.sum + dram__bytes_write.sum", "smsp__inst_executed.sum"), "kernels": {}}
+            for ph, (tms, nl) in phases.items():
+                wi = tj["phases"].get(ph, {}).get("warp_instructions")
+                if wi and tms > 0:
+                    int_issue["kernels"][ph] = {"warp_instructions": wi, "frac": wi * max(nl, 1) / (tms * 1e-3) / ipeak}
+            if dom in int_issue["kernels"]:
+                int_issue["frac"] = int_issue["kernels"][dom]["frac"]
     except Exception:
         pass
     alg = algorithmic_bytes(n, COLS, BLOWUP)
@@ -607,7 +620,8 @@ def run_ours(args):
         "root_matches_cpu_oracle_full_size": (root_hex == gold["cfg2"]) if gold.get("cfg2") else None,
         "phases_ms": {k: round(v[0], 3) for k, v in phases.items()},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": kbytes_launch,
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                     "int_issue_frac": (int_issue or {}).get("frac"), "int_issue": int_issue, "algorithmic_bytes_per_launch": kbytes_launch,
                      "kernel_ms": dom_ms, "launches_per_step": dom_launches,
                      "kernel_share_of_step": phases[dom][0] / ms, "longest_phase": dom_by_time,
                      "kernel_io_bytes": kio_launch, "kernel_io_gbs": kio_launch / (dom_ms * 1e-3) / 1e9,
@@ -630,7 +644,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-log-rows", type=int, default=0, help="rows (log2) of the CPU baseline sample; 0 = 22 when the host has "
-                    ">= 24 threads and >= 96 GB free, else 20")
+                    ">= 16 threads and >= 96 GB free, else 20")
     ap.add_argument("--no-configs", action="store_true", help="skip the cfg4 / cfg5 sub-benchmarks")
     args = ap.parse_args()
     if args.impl == "reference":

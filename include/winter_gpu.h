@@ -28,7 +28,7 @@ extern "C" {
 enum {
   WG_OK = 0,
   WG_ERR_NOT_POW2 = -1,     /* fft/mod.rs:90-105,279-295 "must be a power of 2"; MerkleTreeError::NumberOfLeavesNotPowerOfTwo */
-  WG_ERR_TOO_LARGE = -2,    /* log2(domain) > TWO_ADICITY (fft/mod.rs:291-295) or beyond this build's 2-pass limit (2^24) */
+  WG_ERR_TOO_LARGE = -2,    /* log2(domain) > TWO_ADICITY (fft/mod.rs:291-295) (domain = n * blowup) */
   WG_ERR_ZERO_OFFSET = -3,  /* fft/mod.rs:197-200 "domain offset cannot be zero" */
   WG_ERR_TOO_FEW = -4,      /* MerkleTreeError::TooFewLeaves (crypto/src/merkle/mod.rs:118-120) */
   WG_ERR_ARG = -5,          /* null pointer / bad enum / twiddle length mismatch (fft/mod.rs:283-289) */
@@ -58,6 +58,13 @@ uint64_t wg_launch_count(void);
  * number of timed launches-groups per phase into 6-entry arrays, and clears the records. */
 int wg_profile_enable(int on);
 int wg_profile_read(float* ms_out, uint32_t* count_out);
+
+/* Transforms longer than 2^log_len points are computed with one more decimation step (radix 2..16) around 2^log_len-point
+ * two-pass transforms (csrc/split.cuh); the default, 24, is the two-pass plan's own limit, so this is how lengths up to
+ * the field's two-adicity are reached (fft/mod.rs:291-295). 13 <= log_len <= 24 moves the threshold (a 2^24-row trace
+ * with log_len 22 runs 2^11-point passes instead of 2^12-point ones); 0 only reads it. Returns the previous value or a
+ * negative error code. Process-wide; not meant to be changed while a call is in flight. */
+int wg_set_split_log(int log_len);
 
 /* Test probe: out[i] = op(a[i], b[i]) computed by the device field code (op 0 add, 1 sub, 2 mul in the internal
  * representation, 16+i / 32+i multiply by the order-16 root to the +i / -i, 48 f64 as_int). Host buffers. */

@@ -23,6 +23,7 @@
 #include "hash.cuh"
 #include "hash_kernels.cuh"
 #include "ntt_launch.cuh"
+#include "split.cuh"
 #include "fri.cuh"
 
 namespace wg {
@@ -101,6 +102,7 @@ struct Tables {
   };
   std::map<std::pair<int, int>, Two> tm;                       // (log_n, inv) -> w_N^(+-e) two-level (inv: times n^-1)
   std::map<std::tuple<int, int, uint64_t, uint64_t>, Two> pm;  // (log_n, log_b, offset) -> per-coset powers
+  std::map<std::tuple<int, int, int, uint64_t, uint64_t>, Two> pw;  // (log_root, inv, log_len, scale) -> split.cuh PowTab
 
   static int upload(const std::vector<T>& h, T** out) {
     T* d = nullptr;
@@ -228,6 +230,35 @@ struct Tables {
     *zstride_hi = (long long)nhi;
     return WG_OK;
   }
+
+  // scale * w^k, k < 2^log_len, w = the root of order 2^log_root (inverted if inv), as a two-level table (split.cuh)
+  int get_pow(int log_root, bool inv, int log_len, T scale, Two* out) {
+    std::lock_guard<std::mutex> lk(mu);
+    uint64_t s_lo, s_hi = 0;
+    memcpy(&s_lo, &scale, 8);
+    if (sizeof(T) == 16) memcpy(&s_hi, (const char*)&scale + 8, 8);
+    auto key = std::make_tuple(log_root, (int)inv, log_len, s_lo, s_hi);
+    auto it = pw.find(key);
+    if (it == pw.end()) {
+      if (pw.size() >= 32) {  // keyed by the caller's offset, like pm
+        cudaDeviceSynchronize();
+        for (auto& kv : pw) {
+          cudaFree(kv.second.lo);
+          cudaFree(kv.second.hi);
+        }
+        pw.clear();
+      }
+      Two t;
+      t.lb = (log_len + 1) / 2;
+      std::vector<T> lo((size_t)1 << t.lb), hi((size_t)1 << (log_len - t.lb));
+      fill_two(root(log_root, inv), scale, log_len, t.lb, lo.data(), hi.data());
+      WG_TRY(upload(lo, &t.lo));
+      WG_TRY(upload(hi, &t.hi));
+      it = pw.emplace(key, t).first;
+    }
+    *out = it->second;
+    return WG_OK;
+  }
 };
 
 template <class F>
@@ -331,8 +362,15 @@ static int check_domain(uint64_t n, uint64_t blowup) {
   if (!is_pow2(n) || !is_pow2(blowup)) return fail(WG_ERR_NOT_POW2, "size %llu / blowup %llu must be powers of two", (unsigned long long)n, (unsigned long long)blowup);
   if (n < 2) return fail(WG_ERR_ARG, "transform length must be at least 2");
   if (ilog2(n) + ilog2(blowup) > F::kTwoAdicity) return fail(WG_ERR_TOO_LARGE, "domain 2^%d exceeds the field's two-adicity", ilog2(n) + ilog2(blowup));
-  if (ilog2(n) > 2 * MAX_LOG_S) return fail(WG_ERR_TOO_LARGE, "transform length above 2^%d is not supported by the two-pass plan", 2 * MAX_LOG_S);
   return WG_OK;
+}
+
+// Transforms longer than 2^g_split_log points take an outer decimation step by R = 2^lr <= 16 around 2^(log_n - lr)-point
+// transforms (split.cuh); the inner call splits again when it is still too long. Default: the two-pass plan's limit.
+static std::atomic<int> g_split_log{2 * MAX_LOG_S};
+static inline int split_lr(uint64_t n) {
+  const int over = ilog2(n) - g_split_log.load();
+  return over <= 0 ? 0 : (over < 4 ? over : 4);
 }
 
 // ------------------------------------------------------------------------------------------------ interpolate
@@ -340,14 +378,17 @@ static int check_domain(uint64_t n, uint64_t blowup) {
 // contiguous columns.
 template <class F>
 static uint64_t interpolate_scratch_elems(uint32_t n_cols, uint64_t n) {
+  if (split_lr(n)) return 2 * (uint64_t)n_cols * n;  // the R*C sub-columns and the inner transform's scratch
   return ilog2(n) <= MAX_LOG_S ? 0 : (uint64_t)n_cols * n;
 }
 
+// n <= 2^24 (one or two on-chip passes). d_out == d_in is allowed for two-pass lengths (pass A reads d_in into the scratch).
 template <class F>
-static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, uint64_t n, typename F::T* d_out,
-                                   typename F::T* d_scratch, uint64_t scratch_elems, cudaStream_t stream) {
+static int interpolate_columns_base(const typename F::T* d_in, uint32_t n_cols, uint64_t n, typename F::T* d_out,
+                                    typename F::T* d_scratch, uint64_t scratch_elems, cudaStream_t stream) {
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, 1));
+  if (ilog2(n) > 2 * MAX_LOG_S) return fail(WG_ERR_TOO_LARGE, "transform length above 2^%d needs the split plan", 2 * MAX_LOG_S);
   if (n_cols == 0) return WG_OK;
   if (n_cols > 65535) return fail(WG_ERR_UNSUPPORTED, "more than 65535 columns per call");
   const int log_n = ilog2(n);
@@ -416,17 +457,20 @@ static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, u
 // w_n^j. Natural row order, row-major, pad columns zero (row_matrix.rs:82-133; segments.rs:53-207).
 template <class F>
 static uint64_t lde_scratch_elems(uint32_t n_cols, uint64_t n, uint64_t blowup) {
+  // split plan: the de-interleaved sub-polynomials (n), their LDE (n*B) and the inner LDE's scratch (n*B) per column
+  if (split_lr(n)) return (uint64_t)n_cols * n * (2 * blowup + 1);
   return ilog2(n) <= MAX_LOG_S ? 0 : (uint64_t)n_cols * n * blowup;
 }
 
 template <class F>
-static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, typename F::T offset,
-                   typename F::T* d_lde, uint64_t row_width, typename F::T* d_scratch, uint64_t scratch_elems,
-                   cudaStream_t stream, typename F::T* const* d_peers = nullptr, uint32_t n_peers = 0) {
+static int lde_base(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, typename F::T offset,
+                    typename F::T* d_lde, uint64_t row_width, typename F::T* d_scratch, uint64_t scratch_elems,
+                    cudaStream_t stream, typename F::T* const* d_peers = nullptr, uint32_t n_peers = 0) {
   // d_peers (multi-GPU): row block g of the result, rows [g*L/G, (g+1)*L/G), is written to d_peers[g] (a buffer of
   // L/G x row_width elements, usually peer-mapped memory of GPU g) instead of d_lde; see PassArgs::out_peers.
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, blowup));
+  if (ilog2(n) > 2 * MAX_LOG_S) return fail(WG_ERR_TOO_LARGE, "transform length above 2^%d needs the split plan", 2 * MAX_LOG_S);
   if (n_peers) {
     if (!d_peers || !is_pow2(n_peers) || n_peers > (uint32_t)PassArgs<F>::MAX_PEERS)
       return fail(WG_ERR_ARG, "number of row-block owners must be a power of two <= %d", PassArgs<F>::MAX_PEERS);
@@ -590,6 +634,104 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
   return WG_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ split plan (split.cuh)
+template <class F>
+static PowTab<F> powtab_of(const typename Tables<F>::Two& t) {
+  PowTab<F> p;
+  p.lo = t.lo;
+  p.hi = t.hi;
+  p.lb = (uint32_t)t.lb;
+  return p;
+}
+#define WG_SPLIT_LAUNCH(KERNEL, LR, GRID, BLOCK, ...)                                   \
+  do {                                                                                  \
+    switch (LR) {                                                                       \
+      case 1: KERNEL<F, 1><<<GRID, BLOCK, 0, stream>>>(__VA_ARGS__); break;             \
+      case 2: KERNEL<F, 2><<<GRID, BLOCK, 0, stream>>>(__VA_ARGS__); break;             \
+      case 3: KERNEL<F, 3><<<GRID, BLOCK, 0, stream>>>(__VA_ARGS__); break;             \
+      default: KERNEL<F, 4><<<GRID, BLOCK, 0, stream>>>(__VA_ARGS__); break;            \
+    }                                                                                   \
+    CUDA_TRY(cudaGetLastError());                                                       \
+    g_launches++;                                                                       \
+  } while (0)
+
+template <class F>
+static int interpolate_columns_dev(const typename F::T* d_in, uint32_t n_cols, uint64_t n, typename F::T* d_out,
+                                   typename F::T* d_scratch, uint64_t scratch_elems, cudaStream_t stream) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, 1));
+  const int lr = split_lr(n);
+  if (lr == 0) return interpolate_columns_base<F>(d_in, n_cols, n, d_out, d_scratch, scratch_elems, stream);
+  if (n_cols == 0) return WG_OK;
+  const uint64_t R = (uint64_t)1 << lr, M = n >> lr;
+  uint64_t chunk = d_scratch ? scratch_elems / (2 * n) : 0;
+  if (chunk == 0) return fail(WG_ERR_NOMEM, "interpolation of 2^%d points needs scratch for 2*n elements per column", ilog2(n));
+  if (chunk > 65535 / R) chunk = 65535 / R;
+  typename Tables<F>::Two tw;
+  WG_TRY(tables<F>().get_pow(ilog2(n), true, ilog2(M), F::one(), &tw));
+  const PowTab<F> tab = powtab_of<F>(tw);
+  const T r_inv = f_inv<F>(F::from_u64(R));
+  for (uint64_t c0 = 0; c0 < n_cols; c0 += chunk) {
+    const uint32_t nc = (uint32_t)((n_cols - c0) < chunk ? (n_cols - c0) : chunk);
+    T* e = d_scratch;                 // nc*R sub-columns of M values, transformed in place
+    T* s = d_scratch + (uint64_t)nc * n;
+    const dim3 grid(cdiv(M, 256), nc, 1);
+    {
+      ProfScope ps(PH_INTERP_A, stream);
+      WG_SPLIT_LAUNCH(split_interp_pre_kernel, lr, grid, 256, d_in + c0 * n, e, M, tab, r_inv);
+    }
+    WG_TRY(interpolate_columns_dev<F>(e, (uint32_t)(nc * R), M, e, s, scratch_elems - (uint64_t)nc * n, stream));
+    {
+      ProfScope ps(PH_INTERP_B, stream);
+      WG_SPLIT_LAUNCH(split_interleave_kernel, lr, grid, 256, (const T*)e, d_out + c0 * n, M);
+    }
+  }
+  return WG_OK;
+}
+
+template <class F>
+static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, uint64_t blowup, typename F::T offset,
+                   typename F::T* d_lde, uint64_t row_width, typename F::T* d_scratch, uint64_t scratch_elems,
+                   cudaStream_t stream, typename F::T* const* d_peers = nullptr, uint32_t n_peers = 0) {
+  typedef typename F::T T;
+  WG_TRY(check_domain<F>(n, blowup));
+  const int lr = split_lr(n);
+  if (lr == 0) return lde_base<F>(d_polys, n_cols, n, blowup, offset, d_lde, row_width, d_scratch, scratch_elems, stream, d_peers, n_peers);
+  if (n_peers) return fail(WG_ERR_UNSUPPORTED, "row-block scatter is not available for transforms above 2^%d points", g_split_log.load());
+  if (F::is_zero(offset)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
+  if (!elem_is_canonical<F>(offset)) return fail(WG_ERR_ARG, "domain offset is not a reduced field element");
+  if (row_width < n_cols) return fail(WG_ERR_ARG, "row_width < n_cols");
+  if (n_cols == 0) return WG_OK;
+  const uint64_t R = (uint64_t)1 << lr, M = n >> lr, MB = M * blowup;
+  uint64_t chunk = d_scratch ? scratch_elems / (n * (2 * blowup + 1)) : 0;
+  if (chunk == 0) return fail(WG_ERR_NOMEM, "LDE of 2^%d coefficients needs scratch for (2*blowup + 1)*n elements per column", ilog2(n));
+  if (chunk > 65528 / R) chunk = 65528 / R;
+  typename Tables<F>::Two tw;
+  WG_TRY(tables<F>().get_pow(ilog2(n) + ilog2(blowup), false, ilog2(MB), offset, &tw));
+  const PowTab<F> tab = powtab_of<F>(tw);
+  const T offset_r = f_pow<F>(offset, R);
+  for (uint64_t c0 = 0; c0 < n_cols; c0 += chunk) {
+    const uint32_t nc = (uint32_t)((n_cols - c0) < chunk ? (n_cols - c0) : chunk);
+    const bool last = c0 + nc >= n_cols;
+    const uint32_t nc_out = last ? (uint32_t)(row_width - c0) : nc;  // the last sweep also zeroes the pad columns
+    T* d = d_scratch;                          // nc*R sub-polynomials of M coefficients
+    T* e = d + (uint64_t)nc * n;               // their LDE: [MB][nc*R]
+    T* s = e + (uint64_t)nc * n * blowup;
+    {
+      ProfScope ps(PH_LDE_A, stream);
+      WG_SPLIT_LAUNCH(split_deinterleave_kernel, lr, dim3(cdiv(M, 256), nc, 1), 256, d_polys + c0 * n, d, M);
+    }
+    WG_TRY(lde_dev<F>(d, (uint32_t)(nc * R), M, blowup, offset_r, e, (uint64_t)nc * R, s,
+                      scratch_elems - (uint64_t)nc * n * (blowup + 1), stream));
+    {
+      ProfScope ps(PH_LDE_B, stream);
+      WG_SPLIT_LAUNCH(split_lde_post_kernel, lr, dim3(cdiv(MB, 8), cdiv(nc_out, 32), 1), dim3(32, 8, 1), (const T*)e,
+                      (uint64_t)nc * R, d_lde + c0, row_width, nc, nc_out, MB, tab);
+    }
+  }
+  return WG_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ hashing / Merkle
 template <class F>
 static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes, const uint64_t* row_widths,
@@ -616,19 +758,26 @@ static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes,
   a.unit_off[n_traces] = (uint32_t)off;
   const unsigned blocks = cdiv(rows, 32 * HASH_WARPS);
   ProfScope ps(PH_HASH, stream);
+  const bool multi = off * 8 > 1024, one = n_traces == 1;
+#define WG_HASH_LAUNCH(H, M, O) hash_rows_kernel<F, H, M, O><<<blocks, HASH_WARPS * 32, 0, stream>>>(a)
+#define WG_HASH_PICK(H)                                  \
+  do {                                                   \
+    if (multi && one) WG_HASH_LAUNCH(H, true, true);     \
+    else if (multi) WG_HASH_LAUNCH(H, true, false);      \
+    else if (one) WG_HASH_LAUNCH(H, false, true);        \
+    else WG_HASH_LAUNCH(H, false, false);                \
+  } while (0)
   if (hash == WG_HASH_BLAKE3_256) {
-    if (off * 8 <= 1024)
-      hash_rows_kernel<F, HASH_BLAKE3_256, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
-    else
-      hash_rows_kernel<F, HASH_BLAKE3_256, true><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+    WG_HASH_PICK(HASH_BLAKE3_256);
   } else if (hash == WG_HASH_BLAKE3_192) {
-    if (off * 8 <= 1024)
-      hash_rows_kernel<F, HASH_BLAKE3_192, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
-    else
-      hash_rows_kernel<F, HASH_BLAKE3_192, true><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+    WG_HASH_PICK(HASH_BLAKE3_192);
+  } else if (one) {
+    WG_HASH_LAUNCH(HASH_SHA3_256, false, true);
   } else {
-    hash_rows_kernel<F, HASH_SHA3_256, false><<<blocks, HASH_WARPS * 32, 0, stream>>>(a);
+    WG_HASH_LAUNCH(HASH_SHA3_256, false, false);
   }
+#undef WG_HASH_PICK
+#undef WG_HASH_LAUNCH
   CUDA_TRY(cudaGetLastError());
   g_launches++;
   return WG_OK;
@@ -1618,7 +1767,8 @@ static int interpolate_columns_noalloc(const typename F::T* d_in, uint32_t n_col
   void* scr = nullptr;
   WG_TRY(noalloc_scratch(&scr));
   // pass A writes every one of the n_cols*n scratch elements before pass B reads them: nothing has to start at zero
-  return interpolate_columns_dev<F>(d_in, n_cols, n, d_out, (T*)scr, max_elems, stream);
+  // (the base plan: the split plan of longer transforms builds a table on first use)
+  return interpolate_columns_base<F>(d_in, n_cols, n, d_out, (T*)scr, max_elems, stream);
 }
 
 }  // namespace wg
@@ -1666,6 +1816,15 @@ int wg_shutdown(void) {
 const char* wg_last_error(void) { return g_last_error.c_str(); }
 uint32_t wg_digest_bytes(int hash) { return hash_ok(hash) ? (uint32_t)dlen(hash) : 0u; }
 uint64_t wg_launch_count(void) { return g_launches.load(); }
+
+int wg_set_split_log(int log_len) {
+  const int prev = g_split_log.load();
+  if (log_len == 0) return prev;
+  if (log_len < MAX_LOG_S + 1 || log_len > 2 * MAX_LOG_S)
+    return fail(WG_ERR_ARG, "split threshold 2^%d outside [2^%d, 2^%d]", log_len, MAX_LOG_S + 1, 2 * MAX_LOG_S);
+  g_split_log.store(log_len);
+  return prev;
+}
 
 int wg_debug_field_op(int field, int op, const void* a, const void* b, void* out, uint32_t n) {
   if (!a || !b || !out) return fail(WG_ERR_ARG, "null pointer");

@@ -366,19 +366,7 @@ struct F128 {
     mul64wide(h, K, phi, plo);
     return u128_add(l, T{plo, phi}, carry);
   }
-#if defined(__CUDACC__) && defined(WG_F128_MUL_CALL)
-  // out-of-line product: the ~110-instruction body is inlined ~40 times per pass kernel otherwise, and the f128 kernels
-  // showed 12-18 % instruction-fetch stalls (profiles/r1_ncu_f128_summary.txt)
-  static __device__ __noinline__ T mul_call(T a, T b) { return mul_body(a, b); }
-#endif
   static WG_HD T mul(T a, T b) {
-#if defined(__CUDA_ARCH__) && defined(WG_F128_MUL_CALL)
-    return mul_call(a, b);
-#else
-    return mul_body(a, b);
-#endif
-  }
-  static WG_HD T mul_body(T a, T b) {
 #if defined(__CUDA_ARCH__)
     // 256-bit product from sixteen 32x32->64 products: those with i+j even sit on 64-bit boundaries, those with i+j
     // odd are offset by 32 bits, so each class is summed with 64-bit carry chains and the two sums are merged once.

@@ -34,7 +34,8 @@ struct RowHashArgs {
 constexpr int HASH_WARPS = 8;
 
 // MULTI = rows longer than one 1024-byte BLAKE3 chunk (needs the chaining-value stack)
-template <class F, int HASH, bool MULTI>
+// ONE   = a single matrix (the plain commit_to_rows): no matrix lookup at all, pointer and row pitch are loop invariants
+template <class F, int HASH, bool MULTI, bool ONE>
 __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __grid_constant__ RowHashArgs A) {
   // __grid_constant__: the per-matrix tables are indexed with a run-time matrix number; without it the 1 KB argument
   // struct would be copied to every thread's local memory
@@ -59,31 +60,53 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
   }
   bool sha_done = false;
 
-  uint32_t t_base = 0;  // matrix that holds unit u0: advances monotonically with the slabs (no per-element search from 0)
+  // the matrix that holds unit u0 lives in registers and advances monotonically with the slabs; a slab takes the
+  // indexed-constant path only when it straddles a matrix boundary
+  uint32_t t_base = 0;
+  const uint64_t* cur_p = (const uint64_t*)A.lde[0];
+  uint64_t cur_pitch = (uint64_t)A.row_width[0] * (F::kElemBytes / 8);
+  uint32_t cur_lo = 0, cur_hi = ONE ? units_total : A.unit_off[1];
   // an empty row still takes one (padding-only) block: the digest of the empty input
   for (uint32_t u0 = 0; u0 < units_total || (HASH == HASH_SHA3_256 && !sha_done) || (IS_B3 && nbytes == 0 && u0 == 0);
        u0 += SU) {
     // ---- stage SU units of each of the warp's 32 rows: issue all SU loads first (one long-scoreboard wait per
     // slab instead of one per element), then convert and store
-    if (A.n_traces > 1)
+    if (!ONE && u0 >= cur_hi && u0 < units_total) {
       while (t_base + 1 < A.n_traces && u0 >= A.unit_off[t_base + 1]) t_base++;
+      cur_p = (const uint64_t*)A.lde[t_base];
+      cur_pitch = (uint64_t)A.row_width[t_base] * (F::kElemBytes / 8);
+      cur_lo = A.unit_off[t_base];
+      cur_hi = A.unit_off[t_base + 1];
+    }
     uint64_t vals[SU];
+    const bool straddle = !ONE && u0 + SU > cur_hi && cur_hi < units_total;  // warp-uniform
+    if (!straddle) {
 #pragma unroll
-    for (int it = 0; it < SU; it++) {
-      const int idx = lane + 32 * it;
-      const int r = idx / SU, u = idx - r * SU;
-      const uint32_t gu = u0 + u;
-      const uint64_t row = row0 + r;
-      uint64_t v = 0;
-      if (gu < units_total && row < A.rows) {
-        uint32_t t = t_base;
-        if (A.n_traces > 1)
-          while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
-        const uint32_t lu = gu - A.unit_off[t];
-        const uint64_t* p = (const uint64_t*)A.lde[t];
-        v = __ldg(p + row * A.row_width[t] * (F::kElemBytes / 8) + lu);
+      for (int it = 0; it < SU; it++) {
+        const int idx = lane + 32 * it;
+        const int r = idx / SU, u = idx - r * SU;
+        const uint32_t gu = u0 + u;
+        const uint64_t row = row0 + r;
+        uint64_t v = 0;
+        if (gu < units_total && row < A.rows) v = __ldg(cur_p + row * cur_pitch + (gu - cur_lo));
+        vals[it] = v;
       }
-      vals[it] = v;
+    } else {
+#pragma unroll
+      for (int it = 0; it < SU; it++) {
+        const int idx = lane + 32 * it;
+        const int r = idx / SU, u = idx - r * SU;
+        const uint32_t gu = u0 + u;
+        const uint64_t row = row0 + r;
+        uint64_t v = 0;
+        if (gu < units_total && row < A.rows) {
+          uint32_t t = t_base;
+          while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
+          const uint64_t* p = (const uint64_t*)A.lde[t];
+          v = __ldg(p + row * ((uint64_t)A.row_width[t] * (F::kElemBytes / 8)) + (gu - A.unit_off[t]));
+        }
+        vals[it] = v;
+      }
     }
 #pragma unroll
     for (int it = 0; it < SU; it++) {
