@@ -422,6 +422,7 @@ def run_ours(args):
     from starkpack_winterfell_b200 import _lib
     from starkpack_winterfell_b200 import sharded as sh
     from starkpack_winterfell_b200.device import TraceCommitter
+    from starkpack_winterfell_b200.hostmem import bind_to_gpu_node
 
     sh.dist_init(rank, world, device=local)  # wg_init + (N > 1) the library's own NCCL communicator
     gold = golden_roots()
@@ -459,9 +460,12 @@ def run_ours(args):
         del tc
         torch.cuda.empty_cache()
         _lib.check(_lib.lib().wg_shutdown())
-        e2e = run_e2e(torch, w, dev, steps=min(K, 2), warmup=1)
-        torch.cuda.empty_cache()
-        extra["e2e_resident"] = run_e2e_resident(torch, w, dev, steps=min(K, 2), warmup=1)
+        # pinned host buffers on the GPU's NUMA node (hostmem.py): the host-buffer legs are PCIe-bound
+        with bind_to_gpu_node(local) as numa:
+            e2e = run_e2e(torch, w, dev, steps=min(K, 2), warmup=1)
+            torch.cuda.empty_cache()
+            extra["e2e_resident"] = run_e2e_resident(torch, w, dev, steps=min(K, 2), warmup=1)
+        e2e["host_numa"] = numa.info
         assert extra["e2e_resident"]["root"] == root_hex == e2e["root"], "resident / host-pointer / device-resident roots differ"
     else:
         s0, cnt = sh.shard_columns(COLS, world, rank)
@@ -509,7 +513,9 @@ def run_ours(args):
         del local_cols
         torch.cuda.empty_cache()
         _lib.check(_lib.lib().wg_shutdown())
-        e2e = run_e2e_sharded(torch, w, sh, dev, rank, world, steps=min(K, 2), warmup=1, dist=dist)
+        with bind_to_gpu_node(local) as numa:  # every rank's pinned buffers on ITS GPU's NUMA node
+            e2e = run_e2e_sharded(torch, w, sh, dev, rank, world, steps=min(K, 2), warmup=1, dist=dist)
+        e2e["host_numa_rank0"] = numa.info
         assert e2e["root"] == root_hex, "host-pointer sharded root differs"
         torch.cuda.empty_cache()
         _lib.check(_lib.lib().wg_shutdown())

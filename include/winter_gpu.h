@@ -65,6 +65,13 @@ int wg_profile_read(float* ms_out, uint32_t* count_out);
  * with log_len 22 runs 2^11-point passes instead of 2^12-point ones); 0 only reads it. Returns the previous value or a
  * negative error code. Process-wide; not meant to be changed while a call is in flight. */
 int wg_set_split_log(int log_len);
+/* Inner transform length the split plan aims at (default 2^22: both passes 2^11-point). A transform that must split takes
+ * the radix (<= 16) that leaves inner transforms of this length. In addition the LDE (not the interpolation) of a trace
+ * whose preferred radix is >= 4 -- with the defaults exactly the 2^24-row traces, both of whose passes would be 2^12-point
+ * -- PREFERS the split plan when the scratch it is given holds (2*blowup + 1)*n elements for at least min(n_cols, 8)
+ * columns, and uses the two-pass plan otherwise (2^24 x 32 columns: LDE 92.5 -> 82.4 ms). wg_lde_scratch_elems returns the
+ * preferred size. 24 switches the preference off; 0 only reads. Returns the previous value or a negative error code. */
+int wg_set_split_preferred_log(int log_len);
 
 /* Test probe: out[i] = op(a[i], b[i]) computed by the device field code (op 0 add, 1 sub, 2 mul in the internal
  * representation, 16+i / 32+i multiply by the order-16 root to the +i / -i, 48 f64 as_int). Host buffers. */

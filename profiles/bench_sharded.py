@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--cols", type=int, default=100)
     ap.add_argument("--forms", default="1:1,2:2,2:3,2:4,2:7,3:1,0:0")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--split-pref", type=int, default=0, help="wg_set_split_preferred_log (default 22; 24 = two-pass plan up to 2^24)")
     ap.add_argument("--split-log", type=int, default=0, help="wg_set_split_log: transforms above 2^k take the split plan (default 24)")
     a = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -31,9 +32,11 @@ def main():
     from starkpack_winterfell_b200 import sharded as sh
 
     sh.dist_init(rank, world, device=local)
+    from starkpack_winterfell_b200._lib import lib
     if a.split_log:
-        from starkpack_winterfell_b200._lib import lib
         assert lib().wg_set_split_log(a.split_log) > 0
+    if a.split_pref:
+        assert lib().wg_set_split_preferred_log(a.split_pref) > 0
     n = 1 << a.log_rows
     seed = bench.SEED if a.cols == 100 else bench.SEED5
     s0, cnt = sh.shard_columns(a.cols, world, rank)
@@ -63,7 +66,7 @@ def main():
             roots.add(h.root())
             h.close()
         if rank == 0:
-            print(json.dumps({"n_gpus": world, "rows": n, "cols": a.cols, "asked": form, "split_log": a.split_log or 24, "exchange": used[0], "chunks": used[1], "ms": round(best, 3),
+            print(json.dumps({"n_gpus": world, "rows": n, "cols": a.cols, "asked": form, "split_log": a.split_log or 24, "split_pref": a.split_pref or 22, "exchange": used[0], "chunks": used[1], "ms": round(best, 3),
                               "phases_ms_max_over_ranks": ph_best, "bytes_sent_per_gpu": sent}), flush=True)
     assert len(roots) == 1, "exchange forms disagree on the root"
     if rank == 0:

@@ -17,7 +17,7 @@ ERR_NOT_POW2, ERR_TOO_LARGE, ERR_ZERO_OFFSET, ERR_TOO_FEW, ERR_ARG, ERR_CUDA, ER
 
 # every symbol include/winter_gpu.h declares (tests check the .so exports all of them)
 SYMBOLS = [
-    "wg_init", "wg_shutdown", "wg_last_error", "wg_digest_bytes", "wg_launch_count", "wg_profile_enable", "wg_profile_read", "wg_debug_field_op", "wg_set_split_log", "wg_get_twiddles", "wg_interpolate_poly",
+    "wg_init", "wg_shutdown", "wg_last_error", "wg_digest_bytes", "wg_launch_count", "wg_profile_enable", "wg_profile_read", "wg_debug_field_op", "wg_set_split_log", "wg_set_split_preferred_log", "wg_get_twiddles", "wg_interpolate_poly",
     "wg_interpolate_poly_with_offset", "wg_evaluate_poly", "wg_evaluate_poly_with_offset", "wg_interpolate_columns", "wg_evaluate_polys_over", "wg_hash_rows", "wg_hash_comb_rows", "wg_evaluate_columns_at", "wg_merkle_new",
     "wg_commit_trace", "wg_interpolate_scratch_elems", "wg_lde_scratch_elems", "wg_interpolate_columns_dev",
     "wg_interpolate_columns_noalloc_dev", "wg_lde_dev", "wg_hash_rows_dev", "wg_merkle_dev", "wg_commit_trace_dev",
@@ -64,6 +64,7 @@ def lib():
         L.wg_get_twiddles.argtypes = [i32, u64, i32, vp]
         L.wg_debug_field_op.argtypes = [i32, i32, vp, vp, vp, u32]
         L.wg_set_split_log.argtypes = [i32]
+        L.wg_set_split_preferred_log.argtypes = [i32]
         L.wg_interpolate_poly.argtypes = [i32, vp, u64, vp]
         L.wg_evaluate_poly_with_offset.argtypes = [i32, vp, u64, vp, vp, u64, vp]
         L.wg_interpolate_poly_with_offset.argtypes = [i32, vp, u64, vp, vp]

@@ -368,9 +368,22 @@ static int check_domain(uint64_t n, uint64_t blowup) {
 // Transforms longer than 2^g_split_log points take an outer decimation step by R = 2^lr <= 16 around 2^(log_n - lr)-point
 // transforms (split.cuh); the inner call splits again when it is still too long. Default: the two-pass plan's limit.
 static std::atomic<int> g_split_log{2 * MAX_LOG_S};
-static inline int split_lr(uint64_t n) {
-  const int over = ilog2(n) - g_split_log.load();
+// Inner length the split aims at. 2^12-point passes run one block per SM at 1.3x the per-element cost of 2^11-point ones,
+// so (a) a transform that must split takes the radix that leaves 2^22-point inner transforms (2^25 -> 8 x 2^22, not
+// 2 x 2^24), and (b) the LDE of a 2^24-row trace, whose two passes would both be 2^12-point, PREFERS radix 4 around 2^22
+// when its scratch is there (2^24 x 32 columns on one GPU: LDE 92.5 -> 82.4 ms; a 2^23-row trace has one 2^11-point pass
+// already and loses with radix 2: 78.8 -> 83.7 ms, so a preferred split needs radix >= 4; profiles/r2_split_1gpu.jsonl).
+// The interpolation gains nothing from (b) (12.5 ms either way) and only splits above g_split_log.
+static std::atomic<int> g_split_pref{22};
+static inline int split_target(int log_n) {
+  const int hard = g_split_log.load(), pref = g_split_pref.load();
+  const int over = log_n - (pref < hard ? pref : hard);
   return over <= 0 ? 0 : (over < 4 ? over : 4);
+}
+static inline int split_lr(uint64_t n) { return ilog2(n) > g_split_log.load() ? split_target(ilog2(n)) : 0; }
+static inline int split_lr_pref(uint64_t n) {
+  const int lr = split_target(ilog2(n));
+  return split_lr(n) ? lr : (lr >= 2 ? lr : 0);
 }
 
 // ------------------------------------------------------------------------------------------------ interpolate
@@ -458,6 +471,12 @@ static int interpolate_columns_base(const typename F::T* d_in, uint32_t n_cols, 
 template <class F>
 static uint64_t lde_scratch_elems(uint32_t n_cols, uint64_t n, uint64_t blowup) {
   // split plan: the de-interleaved sub-polynomials (n), their LDE (n*B) and the inner LDE's scratch (n*B) per column
+  if (split_lr_pref(n)) return (uint64_t)n_cols * n * (2 * blowup + 1);
+  return ilog2(n) <= MAX_LOG_S ? 0 : (uint64_t)n_cols * n * blowup;
+}
+// the least the LDE can work with (two-pass plan where it applies): for callers that ran out of memory
+template <class F>
+static uint64_t lde_scratch_elems_min(uint32_t n_cols, uint64_t n, uint64_t blowup) {
   if (split_lr(n)) return (uint64_t)n_cols * n * (2 * blowup + 1);
   return ilog2(n) <= MAX_LOG_S ? 0 : (uint64_t)n_cols * n * blowup;
 }
@@ -695,8 +714,15 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
                    cudaStream_t stream, typename F::T* const* d_peers = nullptr, uint32_t n_peers = 0) {
   typedef typename F::T T;
   WG_TRY(check_domain<F>(n, blowup));
-  const int lr = split_lr(n);
-  if (lr == 0) return lde_base<F>(d_polys, n_cols, n, blowup, offset, d_lde, row_width, d_scratch, scratch_elems, stream, d_peers, n_peers);
+  int lr = split_lr(n);
+  if (lr == 0) {
+    // preferred, not required: only with scratch for at least min(n_cols, 8) columns of the split plan
+    const int lp = split_lr_pref(n);
+    const uint64_t need = n * (2 * blowup + 1) * (n_cols < 8 ? n_cols : 8);
+    if (lp == 0 || n_peers || !d_scratch || scratch_elems < need)
+      return lde_base<F>(d_polys, n_cols, n, blowup, offset, d_lde, row_width, d_scratch, scratch_elems, stream, d_peers, n_peers);
+    lr = lp;
+  }
   if (n_peers) return fail(WG_ERR_UNSUPPORTED, "row-block scatter is not available for transforms above 2^%d points", g_split_log.load());
   if (F::is_zero(offset)) return fail(WG_ERR_ZERO_OFFSET, "domain offset cannot be zero");
   if (!elem_is_canonical<F>(offset)) return fail(WG_ERR_ARG, "domain offset is not a reduced field element");
@@ -725,7 +751,9 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
                       scratch_elems - (uint64_t)nc * n * (blowup + 1), stream));
     {
       ProfScope ps(PH_LDE_B, stream);
-      WG_SPLIT_LAUNCH(split_lde_post_kernel, lr, dim3(cdiv(MB, 8), cdiv(nc_out, 32), 1), dim3(32, 8, 1), (const T*)e,
+      // block = bx columns x (256 / bx) rows; narrow sweeps (an 8-column chunk of a sharded commit) keep every thread busy
+      const unsigned bx = nc_out <= 4 ? 4 : (nc_out <= 8 ? 8 : (nc_out <= 16 ? 16 : 32)), by = 256 / bx;
+      WG_SPLIT_LAUNCH(split_lde_post_kernel, lr, dim3(cdiv(MB, by), cdiv(nc_out, bx), 1), dim3(bx, by, 1), (const T*)e,
                       (uint64_t)nc * R, d_lde + c0, row_width, nc, nc_out, MB, tab);
     }
   }
@@ -1823,6 +1851,15 @@ int wg_set_split_log(int log_len) {
   if (log_len < MAX_LOG_S + 1 || log_len > 2 * MAX_LOG_S)
     return fail(WG_ERR_ARG, "split threshold 2^%d outside [2^%d, 2^%d]", log_len, MAX_LOG_S + 1, 2 * MAX_LOG_S);
   g_split_log.store(log_len);
+  return prev;
+}
+
+int wg_set_split_preferred_log(int log_len) {
+  const int prev = g_split_pref.load();
+  if (log_len == 0) return prev;
+  if (log_len < MAX_LOG_S + 1 || log_len > 2 * MAX_LOG_S)
+    return fail(WG_ERR_ARG, "preferred split threshold 2^%d outside [2^%d, 2^%d]", log_len, MAX_LOG_S + 1, 2 * MAX_LOG_S);
+  g_split_pref.store(log_len);
   return prev;
 }
 

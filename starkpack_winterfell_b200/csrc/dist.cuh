@@ -259,18 +259,28 @@ static int shard_scratch_alloc(const ShardedCommit* h, uint32_t my_cols, bool ne
     shard_chunk(my_cols, h->K, k, &c0, &cc);
     if (cc > maxc) maxc = cc;
   }
-  uint64_t se = interpolate_scratch_elems<F>(my_cols, h->n);
-  const uint64_t se2 = lde_scratch_elems<F>(maxc, h->n, h->blowup);
-  if (se2 > se) se = se2;
-  s->scr_elems = se;
-  s->scr_bytes = se * sizeof(T) + 16;
-  WG_TRY(cached_malloc(&s->scr, s->scr_bytes));
+  // the send buffers first, then the transform scratch: at its preferred size (split plan for 2^23 / 2^24-row traces, see
+  // api.cu g_split_pref) when that still fits, else the two-pass plan's
   if (need_send) {
     s->send_bytes = (size_t)h->L * shard_rw(maxc) * sizeof(T);
     if (s->send_bytes == 0) s->send_bytes = 16;
     WG_TRY(cached_malloc(&s->send[0], s->send_bytes));
     if (h->K > 1) WG_TRY(cached_malloc(&s->send[1], s->send_bytes));
   }
+  const uint64_t se_i = interpolate_scratch_elems<F>(my_cols, h->n);
+  const bool scatter = h->exchange == WG_EXCHANGE_FUSED_P2P && h->world > 1;  // the scatter form keeps the two-pass plan
+  const uint64_t se_min = lde_scratch_elems_min<F>(maxc, h->n, h->blowup);
+  const uint64_t se_pref = scatter ? se_min : lde_scratch_elems<F>(maxc, h->n, h->blowup);
+  for (int attempt = 0; attempt < 2; attempt++) {
+    const uint64_t se_l = attempt == 0 ? se_pref : se_min;
+    s->scr_elems = se_i > se_l ? se_i : se_l;
+    s->scr_bytes = s->scr_elems * sizeof(T) + 16;
+    if (cached_malloc(&s->scr, s->scr_bytes) == WG_OK) return WG_OK;
+    s->scr = nullptr;
+    cudaGetLastError();  // the failed allocation must not surface at the next launch check
+    if (se_pref == se_min) break;
+  }
+  return fail(WG_ERR_NOMEM, "no memory for %zu bytes of transform scratch", s->scr_bytes);
   return WG_OK;
 }
 

@@ -80,7 +80,29 @@ __global__ void __launch_bounds__(HASH_WARPS * 32, 4) hash_rows_kernel(const __g
     }
     uint64_t vals[SU];
     const bool straddle = !ONE && u0 + SU > cur_hi && cur_hi < units_total;  // warp-uniform
-    if (!straddle) {
+    if (IS_B3) {
+      // SU = 16 divides the warp: lane + 32*it is always unit (lane & 15) of row (lane >> 4) + 2*it, so a lane looks its
+      // unit's matrix up ONCE per slab, also when the slab straddles matrices (8-column chunks of a sharded commit
+      // straddle in every slab)
+      const uint32_t gu = u0 + (lane & 15);
+      const uint64_t* p = cur_p;
+      uint64_t pitch = cur_pitch;
+      uint32_t lo = cur_lo;
+      if (straddle && gu >= cur_hi && gu < units_total) {
+        uint32_t t = t_base + 1;
+        while (t + 1 < A.n_traces && gu >= A.unit_off[t + 1]) t++;
+        p = (const uint64_t*)A.lde[t];
+        pitch = (uint64_t)A.row_width[t] * (F::kElemBytes / 8);
+        lo = A.unit_off[t];
+      }
+      p += gu - lo;
+      const uint64_t rbase = row0 + (lane >> 4);
+#pragma unroll
+      for (int it = 0; it < SU; it++) {
+        const uint64_t row = rbase + 2 * it;
+        vals[it] = (gu < units_total && row < A.rows) ? __ldg(p + row * pitch) : 0;
+      }
+    } else if (!straddle) {
 #pragma unroll
       for (int it = 0; it < SU; it++) {
         const int idx = lane + 32 * it;

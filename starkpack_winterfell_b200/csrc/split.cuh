@@ -92,7 +92,8 @@ __global__ void __launch_bounds__(256) split_interp_pre_kernel(const typename F:
 // LDE, last step. e: row-major [MB][rw_e], row k' holds Q_r(x_k'^R) of column c at e[k'*rw_e + c*R + r] (c < nc_in).
 // out: row-major [R*MB][rw_out]; columns c0 + c, c < nc_out: out[(k' + j*MB)*rw_out + c0 + c] = sum_r (x_k' w_R^j)^r e_r
 // for c < nc_in and 0 for the pad columns nc_in <= c < nc_out. tab: x_k' = offset * w_{nB}^k'.
-// block = (32 columns) x (8 rows): stores of a row are contiguous across threadIdx.x.
+// block = (bx columns) x (256 / bx rows), bx chosen by the host from the sweep width: stores of a row are contiguous
+// across threadIdx.x.
 template <class F, int LR>
 __global__ void __launch_bounds__(256) split_lde_post_kernel(const typename F::T* __restrict__ e, uint64_t rw_e,
                                                              typename F::T* __restrict__ out, uint64_t rw_out, uint32_t nc_in,

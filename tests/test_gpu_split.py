@@ -97,6 +97,53 @@ def test_split_offset_evaluation(wg, oracle, split13):
     assert np.array_equal(back, p)
 
 
+def test_preferred_split_for_lde(wg, oracle):
+    """2^23 / 2^24-row LDEs prefer the split plan when the scratch allows (wg_set_split_preferred_log, default 22) and fall
+    back to the two-pass plan otherwise; exercised at 2^15 rows with the preference lowered to 2^13: host entry (scratch at
+    the preferred size), device entry with the two-pass plan's scratch only, and the sharded commit on emulated ranks."""
+    import ctypes as C
+
+    import torch
+
+    from starkpack_winterfell_b200 import sharded
+    from starkpack_winterfell_b200._lib import check, lib
+
+    L = lib()
+    assert L.wg_set_split_preferred_log(0) == 22
+    assert L.wg_set_split_preferred_log(13) == 22
+    try:
+        n, blowup, cols = 1 << 15, 8, 10
+        tr = rand_cols(F64, 985, cols, n)
+        want = oracle.commit_trace(F64, B3, [tr], blowup)
+        polys = wg.matrix.ColMatrix(F64, list(tr)).interpolate_columns()
+        launches0 = L.wg_launch_count()
+        lde = wg.matrix.RowMatrix.evaluate_polys(polys, blowup)
+        assert np.array_equal(lde.data, want["lde"][0])
+        assert L.wg_launch_count() - launches0 == 4  # de-interleave, two passes over 4 x 10 sub-columns, combine
+        # device entry, scratch of the two-pass plan only: same result through the two passes
+        dev = torch.device("cuda", 0)
+        d_polys = torch.from_numpy(np.ascontiguousarray(want["polys"][0]).view(np.int64)).to(dev)
+        rw = 16
+        d_lde = torch.empty((n * blowup, rw), dtype=torch.int64, device=dev)
+        se = cols * n * blowup
+        assert L.wg_lde_scratch_elems(F64, cols, n, blowup) == cols * n * (2 * blowup + 1)
+        scr = torch.empty(se, dtype=torch.int64, device=dev)
+        off = np.array([(7 << 64) % fx.P64], dtype=np.uint64)
+        launches0 = L.wg_launch_count()
+        check(L.wg_lde_dev(F64, C.c_void_p(d_polys.data_ptr()), cols, n, blowup, C.c_void_p(off.ctypes.data),
+                           C.c_void_p(d_lde.data_ptr()), rw, C.c_void_p(scr.data_ptr()), se, None))
+        torch.cuda.synchronize()
+        assert L.wg_launch_count() - launches0 == 2
+        assert np.array_equal(d_lde.cpu().numpy().view(np.uint64), want["lde"][0])
+        # sharded commit on emulated ranks (chunked forms take the split plan, the scatter form the two-pass plan)
+        d_cols = torch.from_numpy(np.ascontiguousarray(tr).view(np.int64)[..., None]).to(dev)
+        for exchange, chunks in ((1, 0), (2, 2), (3, 0)):
+            root, leaves, nodes = sharded.commit_emulated(F64, B3, n, blowup, cols, 2, d_cols, exchange=exchange, chunks=chunks)
+            assert root == bytes(want["root"]) and np.array_equal(nodes, want["nodes"])
+    finally:
+        assert L.wg_set_split_preferred_log(22) == 13
+
+
 def test_beyond_2_24_default_threshold(wg, oracle):
     """a real 2^25-row column (the two-pass plan stops at 2^24): radix-2 step around two 2^24-point transforms"""
     n, blowup = 1 << 25, 2
