@@ -11,10 +11,10 @@ if [ -z "$SKIP_SMALL" ]; then
 timeout 900 $TR --master-port 29621 tests/run_distributed_gpu.py > gpurun_out/dist_small_${N}gpu_${TAG}.log 2>&1
 echo "rc=$?" >> gpurun_out/dist_small_${N}gpu_${TAG}.log; tail -3 gpurun_out/dist_small_${N}gpu_${TAG}.log
 fi
-timeout 600 $TR --master-port 29622 profiles/bench_sharded.py --forms 2:2,2:4,4:1,4:2,4:4,0:0 > gpurun_out/forms_${N}gpu_${TAG}.jsonl 2> gpurun_out/forms_${N}gpu_${TAG}.err
+timeout 600 $TR --master-port 29622 profiles/bench_sharded.py --forms ${FORMS:-2:2,2:4,4:1,4:2,4:4,0:0} > gpurun_out/forms_${N}gpu_${TAG}.jsonl 2> gpurun_out/forms_${N}gpu_${TAG}.err
 echo "rc=$?" >> gpurun_out/forms_${N}gpu_${TAG}.err; tail -2 gpurun_out/forms_${N}gpu_${TAG}.err; cat gpurun_out/forms_${N}gpu_${TAG}.jsonl
 if [ "$N" -ge 4 ]; then
-  timeout 900 $TR --master-port 29623 profiles/bench_sharded.py --log-rows 24 --cols 256 --reps 2 --forms 2:4,4:2,4:4,0:0 > gpurun_out/forms_cfg5_${N}gpu_${TAG}.jsonl 2> gpurun_out/forms_cfg5_${N}gpu_${TAG}.err
+  timeout 900 $TR --master-port 29623 profiles/bench_sharded.py --log-rows 24 --cols 256 --reps 2 --forms ${FORMS5:-2:4,4:2,4:4,0:0} > gpurun_out/forms_cfg5_${N}gpu_${TAG}.jsonl 2> gpurun_out/forms_cfg5_${N}gpu_${TAG}.err
   # the same with the split plan's preference off (two 2^12-point passes)
   timeout 900 $TR --master-port 29624 profiles/bench_sharded.py --log-rows 24 --cols 256 --reps 2 --forms 4:4 --split-pref 24 >> gpurun_out/forms_cfg5_${N}gpu_${TAG}.jsonl 2>> gpurun_out/forms_cfg5_${N}gpu_${TAG}.err
   echo "rc=$?" >> gpurun_out/forms_cfg5_${N}gpu_${TAG}.err; tail -2 gpurun_out/forms_cfg5_${N}gpu_${TAG}.err; cat gpurun_out/forms_cfg5_${N}gpu_${TAG}.jsonl

@@ -133,6 +133,9 @@ struct DistState {
   int rank = 0, world = 1;
   ncclComm_t comm = nullptr;
   cudaStream_t s_comm = nullptr;
+  static constexpr int N_COPY = 4;           // peer copies of one chunk run on several streams = several copy engines
+  cudaStream_t s_copy[N_COPY] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_copy[N_COPY] = {nullptr, nullptr, nullptr, nullptr};
   std::vector<PeerBuf> peer_bufs;
   uint8_t* d_small = nullptr;  // 64-byte slots: IPC handles / barrier tokens
 };
@@ -140,6 +143,10 @@ static DistState g_dist;
 
 static int dist_streams() {
   if (!g_dist.s_comm) CUDA_TRY(cudaStreamCreateWithFlags(&g_dist.s_comm, cudaStreamNonBlocking));
+  for (int i = 0; i < DistState::N_COPY; i++) {
+    if (!g_dist.s_copy[i]) CUDA_TRY(cudaStreamCreateWithFlags(&g_dist.s_copy[i], cudaStreamNonBlocking));
+    if (!g_dist.ev_copy[i]) CUDA_TRY(cudaEventCreateWithFlags(&g_dist.ev_copy[i], cudaEventDisableTiming));
+  }
   if (!g_dist.d_small) CUDA_TRY(cudaMalloc(&g_dist.d_small, 64 * (PassArgs<Gl64>::MAX_PEERS + 64 + 1)));
   return WG_OK;
 }
@@ -396,12 +403,19 @@ static int sharded_commit_run(ShardedCommit* h, const typename F::T* d_cols, typ
         // each slice is contiguous on both sides; owners are visited round-robin from my right-hand neighbour
         const size_t bytes = (size_t)h->rows * rw_k * sizeof(T);
         const ShardBlock& mine_k = h->blocks[(size_t)r * h->K + k];
+        // the G copies of a chunk go out on N_COPY streams (one copy engine each) and join on the exchange stream
+        for (int c = 0; c < DistState::N_COPY; c++) cudaStreamWaitEvent(g_dist.s_copy[c], ev_lde, 0);
         for (uint32_t i = 0; i < G && cc && rc == WG_OK; i++) {
           const uint32_t o = (r + 1 + i) % G;
           T* dst = (T*)g_dist.peer_bufs[h->peer_slot].peers[o] + mine_k.off;
-          if (cudaMemcpyAsync(dst, send + (size_t)o * h->rows * rw_k, bytes, cudaMemcpyDeviceToDevice, sx) != cudaSuccess)
+          if (cudaMemcpyAsync(dst, send + (size_t)o * h->rows * rw_k, bytes, cudaMemcpyDeviceToDevice,
+                              g_dist.s_copy[i % DistState::N_COPY]) != cudaSuccess)
             rc = fail(WG_ERR_CUDA, "peer copy of chunk %u to rank %u: %s", k, o, cudaGetErrorString(cudaGetLastError()));
           if (o != r) h->bytes_sent += bytes;
+        }
+        for (int c = 0; c < DistState::N_COPY; c++) {
+          cudaEventRecord(g_dist.ev_copy[c], g_dist.s_copy[c]);
+          cudaStreamWaitEvent(sx, g_dist.ev_copy[c], 0);
         }
         cudaEventRecord(ev_x[k & 1], sx);
         continue;
