@@ -49,6 +49,7 @@ if __name__ == "__main__":
     else:
         for name in sys.argv[1:]:
             lib = os.path.join(ROOT, "starkpack_winterfell_b200", "variants", f"libwinter_gpu_{name}.so")
-            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--child"], env=dict(os.environ, WG_LIB_PATH=lib), capture_output=True, text=True)
+            env = dict(os.environ) if name == "main" else dict(os.environ, WG_LIB_PATH=lib)  # "main": the product library
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--child"], env=env, capture_output=True, text=True)
             line = [x for x in r.stdout.splitlines() if x.startswith("{")]
             print(line[-1] if line else json.dumps({"lib": name, "error": (r.stderr or r.stdout)[-400:]}), flush=True)

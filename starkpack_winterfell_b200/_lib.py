@@ -19,7 +19,7 @@ ERR_NOT_POW2, ERR_TOO_LARGE, ERR_ZERO_OFFSET, ERR_TOO_FEW, ERR_ARG, ERR_CUDA, ER
 SYMBOLS = [
     "wg_init", "wg_shutdown", "wg_last_error", "wg_digest_bytes", "wg_launch_count", "wg_profile_enable", "wg_profile_read", "wg_debug_field_op", "wg_set_split_log", "wg_set_split_preferred_log", "wg_get_twiddles", "wg_interpolate_poly",
     "wg_interpolate_poly_with_offset", "wg_evaluate_poly", "wg_evaluate_poly_with_offset", "wg_interpolate_columns", "wg_evaluate_polys_over", "wg_hash_rows", "wg_hash_comb_rows", "wg_evaluate_columns_at", "wg_merkle_new",
-    "wg_commit_trace", "wg_interpolate_scratch_elems", "wg_lde_scratch_elems", "wg_interpolate_columns_dev",
+    "wg_commit_trace", "wg_interpolate_scratch_elems", "wg_lde_scratch_elems", "wg_commit_scratch_elems", "wg_interpolate_columns_dev",
     "wg_interpolate_columns_noalloc_dev", "wg_lde_dev", "wg_hash_rows_dev", "wg_merkle_dev", "wg_commit_trace_dev",
     "wg_commit_polys", "wg_commitment_from_trace", "wg_commitment_from_polys", "wg_commitment_info", "wg_commitment_rows",
     "wg_commitment_digests", "wg_commitment_download", "wg_commitment_free",
@@ -80,6 +80,8 @@ def lib():
         L.wg_interpolate_scratch_elems.argtypes = [i32, u32, u64]
         L.wg_lde_scratch_elems.restype = u64
         L.wg_lde_scratch_elems.argtypes = [i32, u32, u64, u64]
+        L.wg_commit_scratch_elems.restype = u64
+        L.wg_commit_scratch_elems.argtypes = [i32, u64, u64, u32, vp]
         L.wg_interpolate_columns_dev.argtypes = [i32, vp, u32, u64, vp, vp, u64, vp]
         L.wg_interpolate_columns_noalloc_dev.argtypes = [i32, vp, u32, u64, vp, vp]
         L.wg_lde_dev.argtypes = [i32, vp, u32, u64, u64, vp, vp, u64, vp, u64, vp]

@@ -760,6 +760,93 @@ static int lde_dev(const typename F::T* d_polys, uint32_t n_cols, uint64_t n, ui
   return WG_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ LDE of several traces
+// StarkPack commits several NARROW traces together (cfg4: 8 fib traces of 2 columns). Extended one by one, each runs partly
+// filled 4-column tiles and its own pair of launches; all columns extended together as one [L][W] matrix fill the tiles, and
+// a memory-bound copy then lays every trace out as its own row-major matrix (what RowMatrix / TraceLde hold,
+// row_matrix.rs:38-45). Taken when it saves more tile columns than the copy costs (the copy moves 2 x 16..32 bytes per
+// element, the LDE costs ~5x that in time) and the scratch holds the combined matrix next to the LDE's own scratch.
+static inline bool traces_prefer_combined(uint32_t n_traces, const uint32_t* cols) {
+  if (n_traces < 2) return false;
+  uint64_t total = 0, tiles = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    total += cols[t];
+    tiles += (cols[t] + 3) / 4;
+  }
+  const uint64_t saved_cols = 4 * tiles - (total + 3) / 4 * 4;
+  return saved_cols * 5 > total;
+}
+template <class F>
+static uint64_t traces_combined_elems(uint32_t n_traces, const uint32_t* cols, uint64_t n, uint64_t blowup) {
+  uint64_t total = 0;
+  for (uint32_t t = 0; t < n_traces; t++) total += cols[t];
+  const uint64_t W = (total + 7) / 8 * 8;
+  return n * blowup * W + lde_scratch_elems<F>((uint32_t)total, n, blowup);
+}
+// scratch for a whole commit of these traces at its fastest plan
+template <class F>
+static uint64_t commit_scratch_elems(uint32_t n_traces, const uint32_t* cols, uint64_t n, uint64_t blowup) {
+  uint64_t total = 0, max_cols = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    total += cols[t];
+    if (cols[t] > max_cols) max_cols = cols[t];
+  }
+  uint64_t se = interpolate_scratch_elems<F>((uint32_t)(total < 65535 ? total : 65535), n);
+  const uint64_t se2 = lde_scratch_elems<F>((uint32_t)max_cols, n, blowup);
+  if (se2 > se) se = se2;
+  if (traces_prefer_combined(n_traces, cols)) {
+    const uint64_t se3 = traces_combined_elems<F>(n_traces, cols, n, blowup);
+    if (se3 > se) se = se3;
+  }
+  return se;
+}
+// dst[row*rw + c] = c < cols ? src[row*W + c] : 0
+template <class T>
+__global__ void __launch_bounds__(256) unpack_trace_kernel(const T* __restrict__ src, uint64_t W, T* __restrict__ dst, uint32_t rw,
+                                                           uint32_t cols, uint64_t rows) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * rw) return;
+  const uint64_t row = i / rw;
+  const uint32_t c = (uint32_t)(i - row * rw);
+  T v;
+  memset(&v, 0, sizeof v);
+  if (c < cols) v = src[row * W + c];
+  dst[i] = v;
+}
+// every trace's LDE into ldes[t] ([L][rws[t]], pad columns zero); after(t) runs once trace t's matrix is enqueued
+template <class F, class After>
+static int lde_traces_dev(const typename F::T* d_polys, uint32_t n_traces, const uint32_t* cols, uint64_t n, uint64_t blowup,
+                          typename F::T offset, void* const* ldes, const uint64_t* rws, typename F::T* d_scratch,
+                          uint64_t scratch_elems, cudaStream_t stream, After after) {
+  typedef typename F::T T;
+  const uint64_t L = n * blowup;
+  uint64_t total = 0;
+  for (uint32_t t = 0; t < n_traces; t++) total += cols[t];
+  const uint64_t W = (total + 7) / 8 * 8, comb = L * W;
+  const uint64_t lde_min = lde_scratch_elems_min<F>((uint32_t)(total < 8 ? total : 8), n, blowup);
+  if (traces_prefer_combined(n_traces, cols) && d_scratch && scratch_elems >= comb + lde_min && total <= 65528) {
+    T* cm = d_scratch;
+    WG_TRY(lde_dev<F>(d_polys, (uint32_t)total, n, blowup, offset, cm, W, d_scratch + comb, scratch_elems - comb, stream));
+    uint64_t c0 = 0;
+    for (uint32_t t = 0; t < n_traces; t++) {
+      ProfScope ps(PH_LDE_B, stream);
+      unpack_trace_kernel<T><<<cdiv(L * rws[t], 256), 256, 0, stream>>>(cm + c0, W, (T*)ldes[t], (uint32_t)rws[t], cols[t], L);
+      CUDA_TRY(cudaGetLastError());
+      g_launches++;
+      c0 += cols[t];
+      WG_TRY(after(t));
+    }
+    return WG_OK;
+  }
+  uint64_t c0 = 0;
+  for (uint32_t t = 0; t < n_traces; t++) {
+    WG_TRY(lde_dev<F>(d_polys + c0 * n, cols[t], n, blowup, offset, (T*)ldes[t], rws[t], d_scratch, scratch_elems, stream));
+    c0 += cols[t];
+    WG_TRY(after(t));
+  }
+  return WG_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ hashing / Merkle
 template <class F>
 static int hash_rows_dev(int hash, uint32_t n_traces, const void* const* d_ldes, const uint64_t* row_widths,
@@ -1000,18 +1087,16 @@ static int commit_trace_dev(int hash, uint64_t n, uint64_t blowup, uint32_t n_tr
     WG_TRY(interpolate_columns_dev<F>(d_cols + c0 * n, nc, n, d_polys + c0 * n, d_scratch, scratch_elems, stream));
   }
   // evaluate_polys_over::<8> per trace (prover/src/lib.rs:641-650), offset = GENERATOR (air/src/options.rs:199-201)
+  // (several narrow traces are extended together when the scratch allows: lde_traces_dev)
   const void* ldes[HASH_MAX_TRACES];
   uint64_t rws[HASH_MAX_TRACES], els[HASH_MAX_TRACES];
-  uint64_t c0 = 0;
   for (uint32_t t = 0; t < n_traces; t++) {
-    const uint64_t rw = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
-    WG_TRY(lde_dev<F>(d_polys + c0 * n, cols_per_trace[t], n, blowup, generator<F>(), (T*)d_ldes[t], rw, d_scratch,
-                      scratch_elems, stream));
     ldes[t] = d_ldes[t];
-    rws[t] = rw;
+    rws[t] = (uint64_t)(cols_per_trace[t] + 7) / 8 * 8;
     els[t] = cols_per_trace[t];
-    c0 += cols_per_trace[t];
   }
+  WG_TRY(lde_traces_dev<F>(d_polys, n_traces, cols_per_trace, n, blowup, generator<F>(), d_ldes, rws, d_scratch, scratch_elems, stream,
+                           [](uint32_t) { return WG_OK; }));
   // commit_to_comb_rows (row_matrix.rs:204-238)
   WG_TRY(hash_rows_dev<F>(hash, n_traces, ldes, rws, els, n * blowup, d_leaves, stream));
   return merkle_dev(hash, d_leaves, n * blowup, d_nodes, stream);
@@ -1346,9 +1431,17 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
   const uint64_t se2 = lde_scratch_elems<F>((uint32_t)max_cols, n, blowup);
   if (se2 > se) se = se2;
   auto al = [](size_t b) { return (b + 255) / 256 * 256; };
-  size_t need = 2 * al(colb * total_cols) + 2 * al(L * dlen(hash)) + al(se * sizeof(T) + 16);
-  for (uint32_t t = 0; t < n_traces; t++) need += al(L * ((uint64_t)(cols_per_trace[t] + 7) / 8 * 8) * sizeof(T));
+  size_t fixed = 2 * al(colb * total_cols) + 2 * al(L * dlen(hash));
+  for (uint32_t t = 0; t < n_traces; t++) fixed += al(L * ((uint64_t)(cols_per_trace[t] + 7) / 8 * 8) * sizeof(T));
   std::lock_guard<std::mutex> lk(g_commit_mu);
+  {
+    // several narrow traces: room for the combined LDE matrix when the device has it (lde_traces_dev)
+    const uint64_t se_fast = commit_scratch_elems<F>(n_traces, cols_per_trace, n, blowup);
+    size_t free_b = 0, total_b = 0;
+    if (se_fast > se && cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && fixed + al(se_fast * sizeof(T) + 16) <= free_b + g_arena_bytes)
+      se = se_fast;
+  }
+  const size_t need = fixed + al(se * sizeof(T) + 16);
   WG_TRY(arena_reserve(need));
   char* cur = g_arena;
   auto take = [&](size_t b) {
@@ -1386,18 +1479,17 @@ static int h_commit_trace(int hash, uint64_t n, uint64_t blowup, uint32_t n_trac
     for (uint64_t c = 0; c < total_cols; c++)
       CUDA_TRY(cudaMemcpyAsync(polys_out[c], (char*)polys + c * colb, colb, cudaMemcpyDeviceToHost, sx));
   }
-  uint64_t c0 = 0;
-  std::vector<const void*> lde_c(n_traces);
-  for (uint32_t t = 0; t < n_traces; t++) {
-    WG_TRY(lde_dev<F>(polys + c0 * n, cols_per_trace[t], n, blowup, generator<F>(), ldes[t], rws[t], scr, se, sc));
-    lde_c[t] = ldes[t];
-    c0 += cols_per_trace[t];
-    if (lde_out && lde_out[t]) {
-      CUDA_TRY(cudaEventRecord(g_ev[1], sc));
-      CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[1], 0));
-      CUDA_TRY(cudaMemcpyAsync(lde_out[t], ldes[t], L * rws[t] * sizeof(T), cudaMemcpyDeviceToHost, sx));
-    }
-  }
+  std::vector<const void*> lde_c(ldes.begin(), ldes.end());
+  std::vector<void*> lde_v(ldes.begin(), ldes.end());
+  WG_TRY(lde_traces_dev<F>(polys, n_traces, cols_per_trace, n, blowup, generator<F>(), lde_v.data(), rws.data(), scr, se, sc,
+                           [&](uint32_t t) -> int {
+                             if (lde_out && lde_out[t]) {  // this trace's D2H rides the copy stream under the next LDE / the hashing
+                               CUDA_TRY(cudaEventRecord(g_ev[1], sc));
+                               CUDA_TRY(cudaStreamWaitEvent(sx, g_ev[1], 0));
+                               CUDA_TRY(cudaMemcpyAsync(lde_out[t], ldes[t], L * rws[t] * sizeof(T), cudaMemcpyDeviceToHost, sx));
+                             }
+                             return WG_OK;
+                           }));
   WG_TRY(hash_rows_dev<F>(hash, n_traces, lde_c.data(), rws.data(), els.data(), L, leaves, sc));
   WG_TRY(merkle_dev(hash, leaves, L, nodes, sc));
   CUDA_TRY(cudaEventRecord(g_ev[2], sc));
@@ -1563,6 +1655,11 @@ static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool
   while (lde_cols > 8 && fixed + lde_scratch_elems<F>((uint32_t)lde_cols, n, blowup) * sizeof(T) > free_b + g_arena_bytes) lde_cols = (lde_cols / 2 + 7) / 8 * 8;
   const uint64_t se2 = lde_scratch_elems<F>((uint32_t)lde_cols, n, blowup);
   if (se2 > se) se = se2;
+  {
+    // several narrow traces: room for the combined LDE matrix when the device has it (lde_traces_dev)
+    const uint64_t se_fast = commit_scratch_elems<F>(n_traces, cm->cols.data(), n, blowup);
+    if (se_fast > se && fixed + al(se_fast * sizeof(T) + 16) <= free_b + g_arena_bytes) se = se_fast;
+  }
   WG_TRY(arena_reserve(fixed + al(se * sizeof(T) + 16)));
   char* cur = g_arena;
   auto take = [&](size_t b) {
@@ -1591,15 +1688,10 @@ static int commitment_build(Commitment* cm, const void* const* column_ptrs, bool
     for (uint64_t c = 0; c < total_cols; c++)
       CUDA_TRY(cudaMemcpyAsync(polys_out[c], (char*)polys + c * colb, colb, cudaMemcpyDeviceToHost, sx));
   }
-  uint64_t c0 = 0;
-  std::vector<const void*> lde_c(n_traces);
-  std::vector<uint64_t> els(n_traces);
-  for (uint32_t t = 0; t < n_traces; t++) {
-    WG_TRY(lde_dev<F>(polys + c0 * n, cm->cols[t], n, blowup, generator<F>(), (T*)cm->ldes[t], cm->rws[t], scr, se, sc));
-    lde_c[t] = cm->ldes[t];
-    els[t] = cm->cols[t];
-    c0 += cm->cols[t];
-  }
+  std::vector<const void*> lde_c(cm->ldes.begin(), cm->ldes.end());
+  std::vector<uint64_t> els(cm->cols.begin(), cm->cols.end());
+  WG_TRY(lde_traces_dev<F>(polys, n_traces, cm->cols.data(), n, blowup, generator<F>(), cm->ldes.data(), cm->rws.data(), scr, se, sc,
+                           [](uint32_t) { return WG_OK; }));
   WG_TRY(hash_rows_dev<F>(cm->hash, n_traces, lde_c.data(), cm->rws.data(), els.data(), L, cm->leaves, sc));
   WG_TRY(merkle_dev(cm->hash, cm->leaves, L, cm->nodes, sc));
   if (root_out) CUDA_TRY(cudaMemcpyAsync(root_out, cm->nodes + dlen(cm->hash), dlen(cm->hash), cudaMemcpyDeviceToHost, sc));
@@ -2110,6 +2202,11 @@ uint64_t wg_interpolate_scratch_elems(int field, uint32_t n_cols, uint64_t n) {
 uint64_t wg_lde_scratch_elems(int field, uint32_t n_cols, uint64_t n, uint64_t blowup) {
   if (!is_pow2(n)) return 0;
   return field == WG_FIELD_F64 ? lde_scratch_elems<Gl64>(n_cols, n, blowup) : lde_scratch_elems<F128>(n_cols, n, blowup);
+}
+uint64_t wg_commit_scratch_elems(int field, uint64_t n_rows, uint64_t blowup, uint32_t n_traces, const uint32_t* cols_per_trace) {
+  if (!cols_per_trace || n_traces == 0 || !is_pow2(n_rows) || !is_pow2(blowup)) return 0;
+  return field == WG_FIELD_F64 ? commit_scratch_elems<Gl64>(n_traces, cols_per_trace, n_rows, blowup)
+                               : commit_scratch_elems<F128>(n_traces, cols_per_trace, n_rows, blowup);
 }
 
 int wg_interpolate_columns_dev(int field, const void* d_cols, uint32_t n_cols, uint64_t n, void* d_polys, void* d_scratch,

@@ -33,9 +33,12 @@ class TraceCommitter:
         self.ldes = [torch.empty((L, rw, w), **kw) for rw in self.row_widths]
         self.leaves = torch.empty((L, 32), dtype=torch.uint8, device=self.device)
         self.nodes = torch.empty((L, 32), dtype=torch.uint8, device=self.device)
-        se = lib().wg_interpolate_scratch_elems(field, tc, n_rows)
-        sc = max(self.cols_per_trace) if lde_scratch_cols is None else lde_scratch_cols
-        se = max(se, lib().wg_lde_scratch_elems(field, sc, n_rows, blowup))
+        self._cpt = (C.c_uint32 * len(self.cols_per_trace))(*self.cols_per_trace)
+        if lde_scratch_cols is None:
+            # the fastest plan's scratch (several narrow traces are extended together: wg_commit_scratch_elems)
+            se = lib().wg_commit_scratch_elems(field, n_rows, blowup, len(self.cols_per_trace), self._cpt)
+        else:
+            se = max(lib().wg_interpolate_scratch_elems(field, tc, n_rows), lib().wg_lde_scratch_elems(field, lde_scratch_cols, n_rows, blowup))
         self.scratch_elems = int(se)
         self.scratch = torch.empty((max(self.scratch_elems, 1), w), **kw)
         self._cpt = (C.c_uint32 * len(self.cols_per_trace))(*self.cols_per_trace)

@@ -78,3 +78,34 @@ def test_commit_to_comb_rows_over_built_ldes(wg, oracle, field, hash_id):
     assert tree.root() == bytes(want["root"])
     with pytest.raises(AssertionError):
         ldes[1].commit_to_comb_rows(hash_id, ldes)  # self must be traces_lde[0]
+
+
+@pytest.mark.parametrize("field,shapes,n", [(1, [2] * 8, 4096), (0, [3, 1, 5, 2], 8192), (0, [2, 2], 256)])
+def test_narrow_traces_extended_together(wg, oracle, field, shapes, n):
+    """StarkPack commits several narrow traces at once (examples/src/do_work: 8 traces of 2 columns). With the scratch of
+    wg_commit_scratch_elems the device entry extends all columns together (full column tiles) and lays every trace out as its
+    own matrix afterwards; with the per-trace scratch it extends them one by one. Same polys, LDE matrices (pad columns
+    zero), leaves and tree as the oracle either way."""
+    import torch
+
+    from starkpack_winterfell_b200._lib import lib
+    from starkpack_winterfell_b200.device import TraceCommitter
+
+    blowup = 8
+    traces = [(fx.synth_f64 if field == 0 else fx.synth_f128)(700 + 3 * i + c, c, n) for i, c in enumerate(shapes)]
+    want = oracle.commit_trace(field, 0, traces, blowup)
+    allc = np.concatenate([np.ascontiguousarray(t) for t in traces], axis=0).view(np.int64)
+    launches = []
+    for per_trace_scratch in (None, max(shapes)):
+        tc = TraceCommitter(field, 0, n, blowup, shapes, device="cuda:0", lde_scratch_cols=per_trace_scratch)
+        tc.cols.copy_(torch.from_numpy(allc if field == 1 else allc[..., None]))
+        l0 = lib().wg_launch_count()
+        tc.commit()
+        torch.cuda.synchronize()
+        launches.append(lib().wg_launch_count() - l0)
+        assert tc.root() == bytes(want["root"])
+        assert np.array_equal(tc.nodes.cpu().numpy(), want["nodes"])
+        for t in range(len(shapes)):
+            got = tc.ldes[t].cpu().numpy().view(np.uint64)
+            assert np.array_equal(got.reshape(want["lde"][t].shape), want["lde"][t]), (per_trace_scratch, t)
+    assert launches[0] != launches[1]  # the two plans really differ
