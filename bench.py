@@ -393,9 +393,11 @@ def run_config_sharded(torch, w, sh, dist, dev, rank, world, name, field, hash_i
     torch.cuda.empty_cache()
     esize = 8 if field == w.F64 else 16
     alg = algorithmic_bytes(n, total_cols, BLOWUP, esize)
+    gbs = alg / world / (best * 1e-3) / 1e9
     return {"config": name, "rows": n, "total_cols": total_cols, "n_gpus": world, "ms": best, "exchange": ex, "chunks": k,
             "phases_ms_rank0": {a: round(b, 3) for a, b in ph.items()}, "bytes_sent_rank0": sent, "root": root.hex(),
-            "algorithmic_bytes": alg, "hbm_gbs_per_gpu": alg / world / (best * 1e-3) / 1e9}
+            "lde_rows_per_s": n * BLOWUP / (best * 1e-3), "trace_rows_per_s": n / (best * 1e-3),
+            "algorithmic_bytes": alg, "hbm_gbs_per_gpu": gbs, "hbm_frac_per_gpu": gbs / peaks()[0]}
 
 
 # ---------------------------------------------------------------------------------------------------------- our arm
@@ -443,14 +445,15 @@ def run_ours(args):
         _lib.profile_read()
         sampler.start()
         launches0 = _lib.launch_count()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
         torch.cuda.synchronize()
-        e0.record()
-        for _ in range(K):
+        evs[0].record()
+        for i in range(K):
             tc.commit()
-        e1.record()
+            evs[i + 1].record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / K
+        ms = evs[0].elapsed_time(evs[K]) / K
+        per_step = [evs[i].elapsed_time(evs[i + 1]) for i in range(K)]
         launches = _lib.launch_count() - launches0
         clocks = sampler.stop()
         phases = {k: (v[0] / K, v[1] // K) for k, v in _lib.profile_read().items()}
@@ -482,12 +485,15 @@ def run_ours(args):
             sampler.start()
         launches0 = _lib.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
         dist.barrier()
         torch.cuda.synchronize()
         e0.record()
+        evs[0].record()
         shard_ph, sent, ex, chunks = {}, 0, None, 0
-        for _ in range(K):
+        for i in range(K):
             h = sh.commit_dev(w.F64, w.BLAKE3_256, n, BLOWUP, COLS, local_cols)
+            evs[i + 1].record()
             ph, sent = h.phases_ms()
             for a, b in ph.items():
                 shard_ph[a] = shard_ph.get(a, 0.0) + b / K
@@ -498,6 +504,9 @@ def run_ours(args):
         torch.cuda.synchronize()
         dist.barrier()
         ms = _max_over_ranks(torch, dist, dev, e0.elapsed_time(e1) / K)
+        ps = torch.tensor([evs[i].elapsed_time(evs[i + 1]) for i in range(K)], device=dev, dtype=torch.float64)
+        dist.all_reduce(ps, op=dist.ReduceOp.MAX)
+        per_step = ps.tolist()
         launches = _lib.launch_count() - launches0
         clocks = sampler.stop() if rank == 0 else None
         phases = {k: (v[0] / K, v[1] // K) for k, v in _lib.profile_read().items()}
@@ -559,6 +568,24 @@ def run_ours(args):
                                 w.BLAKE3_256, n20, 16, cfg4_local)
         c4["matches_oracle_root"] = (c4["root"] == gold["cfg4"]) if gold.get("cfg4") else None
         configs.append(c4)
+        if world == 1:
+            # cfg1 / cfg3: one narrow f128 trace each (2 and 4 columns): they do not shard, so they are timed on one GPU only
+            c1 = run_config_sharded(torch, w, sh, dist, dev, rank, world, "cfg1 fib: f128 2^20 x 2, Blake3_256", w.F128, w.BLAKE3_256, n20, 2,
+                                    lambda s0, cnt: fib_trace_words(torch, n20, (1, 1), dev)[s0:s0 + cnt].contiguous())
+            c1["matches_oracle_root"] = (c1["root"] == gold["cfg1"]) if gold.get("cfg1") else None
+            configs.append(c1)
+            from tests import fixtures as fx
+            import numpy as np
+
+            t3 = torch.from_numpy(np.ascontiguousarray(fx.synth_f128(0xC0FFEE03, 4, n20)).view(np.int64)).to(dev)
+            c3 = run_config_sharded(torch, w, sh, dist, dev, rank, world, "cfg3 rescue shape: f128 2^20 x 4, Sha3_256", w.F128, w.SHA3_256, n20, 4,
+                                    lambda s0, cnt: t3[s0:s0 + cnt].contiguous())
+            c3["matches_oracle_root"] = (c3["root"] == gold["cfg3"]) if gold.get("cfg3") else None
+            configs.append(c3)
+            del t3
+        else:
+            configs.append({"config": "cfg1 fib / cfg3 rescue shape (one f128 trace of 2 / 4 columns)", "n_gpus": world,
+                            "skipped": "a single narrow trace does not shard (fewer column tiles than GPUs): replicas only; timed at N = 1"})
         if world >= 4:
             n24 = 1 << 24
             c5 = run_config_sharded(torch, w, sh, dist, dev, rank, world, "cfg5 big: f64 2^24 x 256", w.F64, w.BLAKE3_256, n24, 256,
@@ -619,6 +646,7 @@ def run_ours(args):
         "metric": METRIC, "value": ms, "unit": "ms", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms,
         "higher_is_better": False, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": workload_config(world),
+        "ms_min": min(per_step), "ms_median": sorted(per_step)[len(per_step) // 2],
         "lde_rows_per_s": L / (ms * 1e-3), "trace_rows_per_s": n / (ms * 1e-3),
         "commit_roofline": {"algorithmic_bytes": alg, "achieved_gbs_per_gpu": alg / world / (ms * 1e-3) / 1e9,
                             "frac_per_gpu": alg / world / (ms * 1e-3) / 1e9 / peak},

@@ -291,7 +291,8 @@ int wg_lde_scatter_dev(int field, const void* d_polys, uint32_t n_cols, uint64_t
  *   WG_EXCHANGE_P2P_COPY   chunked like PIPELINED, but every rank PUSHES its slices into the owners' receive buffers
  *                          (peer-mapped with CUDA IPC) with cudaMemcpyAsync: copy engines over NVLink, no SM used by the
  *                          exchange, one 4-byte NCCL all-gather as the barrier behind the copies (single node);
- *   WG_EXCHANGE_AUTO       fused up to 8 columns per rank (G <= 8), P2P_COPY in 8-column chunks (at most 4) otherwise. */
+ *   WG_EXCHANGE_AUTO       fused up to 8 columns per rank (G <= 8), P2P_COPY in 8-column chunks otherwise (at most 4 chunks; 8 from
+ *                          2^26 LDE rows, which wg_shard_plan cannot know: wg_sharded_info reports the plan a commit used). */
 #define WG_DIST_ID_BYTES 128
 enum { WG_EXCHANGE_AUTO = 0, WG_EXCHANGE_ALLTOALL = 1, WG_EXCHANGE_PIPELINED = 2, WG_EXCHANGE_FUSED_P2P = 3, WG_EXCHANGE_P2P_COPY = 4 };
 #define WG_SHARD_MAX_BLOCKS 64 /* received column blocks (ranks x chunks) the leaf kernel concatenates */

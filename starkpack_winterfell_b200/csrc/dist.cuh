@@ -27,7 +27,8 @@ static inline void shard_chunk(uint32_t cols, uint32_t k, uint32_t idx, uint32_t
   *start = s < cols ? (uint32_t)s : cols;
   *count = s < cols ? (cols - (uint32_t)s < per ? cols - (uint32_t)s : per) : 0;
 }
-static inline void shard_plan(uint32_t total_cols, uint32_t world, int exchange, uint32_t chunks, int* ex_out, uint32_t* k_out) {
+static inline void shard_plan(uint32_t total_cols, uint32_t world, int exchange, uint32_t chunks, int* ex_out, uint32_t* k_out,
+                              uint64_t lde_rows = 0) {
   const uint32_t per_rank = (total_cols + world - 1) / world;
   int ex = exchange;
   uint32_t k = chunks;
@@ -46,7 +47,13 @@ static inline void shard_plan(uint32_t total_cols, uint32_t world, int exchange,
   }
   if (ex == WG_EXCHANGE_FUSED_P2P || ex == WG_EXCHANGE_ALLTOALL) k = 1;
   if (ex == WG_EXCHANGE_PIPELINED || ex == WG_EXCHANGE_P2P_COPY) {
-    if (k == 0) k = per_rank >= 25 ? 4 : (per_rank + 7) / 8;  // 8-column chunks, at most 4: the last chunk's exchange is the exposed one
+    // 8-column chunks; the last chunk's exchange is the exposed one, every chunk costs the LDE a little. At most 4 chunks
+    // (headline on 2 GPUs, 50 columns per rank: x4 44.1 ms, x7 45.3 ms), 8 for traces of 2^26 LDE rows and more, where a
+    // 16-column chunk is 13 GB on the wire (cfg5 on 4 GPUs: 20 ms exposed with x4)
+    if (k == 0) {
+      const uint32_t cap = lde_rows >= ((uint64_t)1 << 26) ? 8 : 4;
+      k = (per_rank + 7) / 8 > cap ? cap : (per_rank + 7) / 8;
+    }
     const uint32_t max_k = (per_rank + 7) / 8;  // at least 8 columns per chunk
     if (k > max_k) k = max_k;
     while (k > 1 && world * k > WG_SHARD_MAX_BLOCKS) k--;
@@ -497,7 +504,7 @@ static int sharded_commit_create(int field, int hash, uint64_t n, uint64_t blowu
   h->total_cols = total_cols;
   int ex;
   uint32_t k;
-  shard_plan(total_cols, G, exchange, chunks, &ex, &k);
+  shard_plan(total_cols, G, exchange, chunks, &ex, &k, h->L);
   h->exchange = ex;
   h->K = k;
   int rc = field == WG_FIELD_F64 ? sharded_commit_run<Gl64>(h, (const uint64_t*)d_cols, (uint64_t*)d_polys, root_out, sc)

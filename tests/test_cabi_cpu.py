@@ -72,6 +72,7 @@ def test_shard_partition_helpers_host_only():
     # auto plan: fused for narrow shards on <= 8 ranks, pipelined otherwise, never more than 64 received blocks
     assert sharded.shard_plan(16, 8) == (_lib.EXCHANGE_FUSED_P2P, 1)
     assert sharded.shard_plan(100, 2) == (_lib.EXCHANGE_P2P_COPY, 4)
+    assert sharded.shard_plan(256, 4) == (_lib.EXCHANGE_P2P_COPY, 4)  # 8 inside a commit of >= 2^26 LDE rows
     assert sharded.shard_plan(100, 8) == (_lib.EXCHANGE_P2P_COPY, 2)
     assert sharded.shard_plan(256, 8) == (_lib.EXCHANGE_P2P_COPY, 4)
     assert sharded.shard_plan(100, 8, _lib.EXCHANGE_PIPELINED) == (_lib.EXCHANGE_PIPELINED, 2)
