@@ -170,7 +170,13 @@ struct FieldCfg<F128> {
   static constexpr int PAD_LOG = 2;  // 4 elements = 64 B
   static constexpr bool L1_FINE = false;
   static constexpr bool SKIP_DEAD = true;  // 2-column fib traces fill half a tile (BASELINE configs 1 and 4)
-  static constexpr int MIN_BLOCKS = 1;
+  // two resident blocks per SM: the 64-register cap costs ~48 bytes of spills per thread and hides the block barriers of
+  // the half-filled tiles of 2-column traces (cfg1 2.85 -> 2.72 ms, profiles/r2_ab_f128_minb2.jsonl); 2^12-point passes
+  // still run one block per SM (128 KB tiles)
+#ifndef WG_F128_MINB
+#define WG_F128_MINB 2
+#endif
+  static constexpr int MIN_BLOCKS = WG_F128_MINB;
 };
 
 template <class F, int LOG_S, int LAYOUT>
