@@ -91,3 +91,40 @@ def test_shard_partition_helpers_host_only():
             m = 1 << (i.bit_length() - 1)
             per = m // G
             assert r == (i - m) // per and li == per + (i - m) % per and 1 <= li < rows
+
+
+def test_scratch_queries_and_split_thresholds_host_only():
+    """The scratch-size queries and the split-plan thresholds are host-only: the sizes a caller allocates from must match
+    the plan the library will run (two-pass up to 2^24; split plan preferred for the LDE of 2^24-row traces and required
+    above; several narrow traces extended together)."""
+    import ctypes as C
+
+    from starkpack_winterfell_b200 import _lib
+
+    L = _lib.lib()
+    F64, F128 = 0, 1
+    assert L.wg_set_split_log(0) == 24 and L.wg_set_split_preferred_log(0) == 22
+    assert L.wg_set_split_log(12) == _lib.ERR_ARG and L.wg_set_split_preferred_log(25) == _lib.ERR_ARG
+    n22, n23, n24, n25 = 1 << 22, 1 << 23, 1 << 24, 1 << 25
+    # one on-chip pass needs no scratch; two passes one intermediate of the output's size
+    assert L.wg_interpolate_scratch_elems(F64, 7, 4096) == 0 and L.wg_lde_scratch_elems(F64, 7, 4096, 8) == 0
+    assert L.wg_interpolate_scratch_elems(F64, 100, n22) == 100 * n22
+    assert L.wg_lde_scratch_elems(F64, 100, n22, 8) == 100 * n22 * 8
+    # 2^23 rows keep the two-pass plan (radix 2 loses), 2^24 rows prefer radix 4 around 2^22: (2B + 1) n per column
+    assert L.wg_lde_scratch_elems(F64, 32, n23, 8) == 32 * n23 * 8
+    assert L.wg_lde_scratch_elems(F64, 32, n24, 8) == 32 * n24 * 17
+    assert L.wg_interpolate_scratch_elems(F64, 32, n24) == 32 * n24  # the interpolation only splits above 2^24
+    assert L.wg_interpolate_scratch_elems(F64, 2, n25) == 2 * 2 * n25 and L.wg_lde_scratch_elems(F64, 2, n25, 2) == 2 * n25 * 5
+    assert L.wg_set_split_preferred_log(24) == 22
+    try:
+        assert L.wg_lde_scratch_elems(F64, 32, n24, 8) == 32 * n24 * 8  # preference off
+    finally:
+        assert L.wg_set_split_preferred_log(22) == 24
+    # whole commits: 8 traces of 2 columns are extended together (combined [L][16] matrix + its LDE scratch), one wide
+    # trace is not
+    n20 = 1 << 20
+    cpt = (C.c_uint32 * 8)(*([2] * 8))
+    assert L.wg_commit_scratch_elems(F128, n20, 8, 8, cpt) == n20 * 8 * 16 + 16 * n20 * 8
+    one = (C.c_uint32 * 1)(100)
+    assert L.wg_commit_scratch_elems(F64, n22, 8, 1, one) == 100 * n22 * 8
+    assert L.wg_commit_scratch_elems(F64, n22, 8, 0, one) == 0 and L.wg_commit_scratch_elems(F64, n22 + 1, 8, 1, one) == 0
