@@ -52,7 +52,7 @@ def main():
         args = args[2:]
     for name in args:
         lib = os.path.join(ROOT, "starkpack_winterfell_b200", "variants", f"libwinter_gpu_{name}.so")
-        env = dict(os.environ, WG_LIB_PATH=lib)
+        env = dict(os.environ) if name == "main" else dict(os.environ, WG_LIB_PATH=lib)  # "main": the product library
         r = subprocess.run([sys.executable, os.path.abspath(__file__), "--child", str(log_rows), str(cols)], env=env, capture_output=True, text=True)
         line = [x for x in r.stdout.splitlines() if x.startswith("{")]
         print(line[-1] if line else json.dumps({"lib": name, "error": (r.stderr or r.stdout)[-400:]}), flush=True)
